@@ -1,0 +1,72 @@
+"""Orchestration (L5): the body of every variant's ``main.py``.
+
+Sequence mirrors ``Balanced All-Reduce/main.py:17-79``: init process group → build
+model → Xavier init → rank-0 broadcast → loaders (timing probe + sharding) →
+optimizer/scheduler → ``train_global`` → rank-0 test evaluation + graphs → teardown;
+with save/resume and the fused-exchange bring-up added.
+"""
+from __future__ import annotations
+
+import sys
+from typing import Optional
+
+import numpy as np
+
+from . import data as D
+from .config import Config, parse_args
+from .engine import make_engine
+from .launch import init_runtime, shutdown
+from .parallel import make_exchanger
+from .trainer import TrainHistory, evaluate, train_global
+from .utils import checkpoint as ckpt
+from .utils import viz
+
+
+def run(cfg: Config) -> TrainHistory:
+    rt = init_runtime(cfg.backend, cfg.seed)
+    try:
+        return _run(cfg, rt)
+    finally:
+        shutdown(rt)
+
+
+def _run(cfg: Config, rt) -> TrainHistory:
+    engine = make_engine(cfg, rt)
+    bundle = D.get_data(cfg, rt.rank)
+    # exchange bring-up first: the broadcast is the first thing that uses it
+    exchanger = make_exchanger(cfg, rt, engine, shard_weights=None)
+    exchanger.broadcast_state(engine, src=0)
+
+    shards = D.initial_shards(bundle, cfg, rt, engine)
+    if cfg.aggregation_type == "shard":
+        # shard-weighted averaging: w_r = n_r / Σn from the actual shard sizes
+        sizes = D.all_gather_floats(float(len(shards.train_indices)), rt)
+        exchanger.set_shard_weights([s / max(sum(sizes), 1.0) for s in sizes])
+
+    history = TrainHistory()
+    start_epoch = 0
+    if cfg.resume:
+        start_epoch = ckpt.load_checkpoint(cfg.resume, engine, history, shards)
+        engine.params_changed()
+
+    def on_epoch_end(ge, h, sh):
+        if cfg.save and rt.rank == 0:
+            ckpt.save_checkpoint(cfg.save, engine, h, sh, epoch=ge + 1, cfg=cfg)
+
+    history = train_global(engine, bundle, shards, cfg, rt, exchanger, history, start_epoch, on_epoch_end)
+
+    if rt.rank == 0:
+        test_loader = D.Loader(bundle.testset, None, cfg.batch_size)
+        evaluate(engine, test_loader, rt, bundle.num_classes, verbose=not cfg.quiet)
+        viz.write_all(history, cfg, rank=rt.rank)
+    exchanger.close()
+    return history
+
+
+def main(argv=None, topology: Optional[str] = None, balance: Optional[str] = None) -> TrainHistory:
+    cfg = parse_args(argv, topology, balance)
+    return run(cfg)
+
+
+if __name__ == "__main__":
+    main(sys.argv[1:])

@@ -1,0 +1,51 @@
+"""Six directory entrypoints on synthetic data over gloo (BASELINE config 1 plumbing),
+checkpoint round-trip, graphs."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT, free_port
+
+VARIANTS = ["Balanced All-Reduce", "Balanced Ring", "Balanced Double-Ring",
+            "Disbalanced All-Reduce", "Disbalanced Ring", "Disalanced Double-Ring"]
+SMALL = ["--synthetic", "--synthetic_train", "192", "--synthetic_val", "64", "--synthetic_test", "64",
+         "--epochs_global", "2", "--epochs_local", "1", "--batch_size", "32", "--probe_batches", "1",
+         "--model", "enhanced_cnn", "--seed", "3", "--quiet"]
+
+
+def launch(variant, nproc, extra, cwd_out):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(free_port()),
+           os.path.join(ROOT, variant, "main.py")] + SMALL + ["--output_folder", str(cwd_out)] + extra
+    env = dict(os.environ, OMP_NUM_THREADS="2", LDNN_TINY_WIDTHS="1")
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    return r
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_variant_runs_two_ranks(variant, tmp_path):
+    out = tmp_path / "Graphs"
+    extra = ["--aggregation_by", "weights"] if "Ring" in variant else []
+    launch(variant, 2, extra, out)
+    for f in ["loss_distribution_by_worker.png", "loss_distribution_per_epoch.png",
+              "loss_distribution_per_epoch_global.png", "accuracy_distribution_per_epoch_global.png",
+              "training_metrics.png", "training_metrics_0.png", "time_throughput.png", "metrics.json"]:
+        assert (out / f).exists() and (out / f).stat().st_size > 0, f
+
+
+def test_step_sync_shard_weighted_and_resume(tmp_path):
+    out, ck = tmp_path / "G", tmp_path / "ck.pt"
+    launch("Disbalanced Ring", 2, ["--sync", "step", "--aggregation_type", "shard", "--shard_ratios", "3", "1",
+                                    "--save", str(ck)], out)
+    blob = torch.load(ck, weights_only=False)
+    assert len(blob["model"]) == 128 and blob["epoch"] == 2
+    assert blob["model"]["layer4.1.conv2.weight"].dtype == torch.float32
+    assert len(blob["indices"]["train"]) > 0
+    # resume: one more global epoch
+    launch("Disbalanced Ring", 2, ["--sync", "step", "--aggregation_type", "shard", "--shard_ratios", "3", "1",
+                                    "--resume", str(ck), "--epochs_global", "3"], out)
