@@ -1,0 +1,440 @@
+// Batch-norm (training + eval) fused with residual add and ReLU, on NHWC bf16  (K-BN-F / K-BN-B),
+// the 3-channel stem's fused cast+im2col, and NHWC max-pool.
+//
+// Replaces ATen/cuDNN BatchNorm2d + F.relu + `out += shortcut(x)`
+// (Balanced All-Reduce/model.py:56,58,64,68-71,79-80).  Statistics are reduced in two levels
+// without atomics on data: every CTA writes per-channel partials for its pixel chunk, takes a
+// ticket, and the last CTA to arrive folds the partials in a fixed order (deterministic), updates
+// the running stats and emits scale/shift — so a BN forward is two launches (stats, apply) and a
+// BN backward is two launches (reduce, apply) regardless of channel count.
+#include "../include/ldnn_b200.h"
+#include "common.cuh"
+#include <atomic>
+
+namespace ldnn {
+extern std::atomic<unsigned long long> g_launches;
+
+constexpr int kBnThreads = 256;
+
+// thread layout shared by the reduction kernels: 8 channels per thread, C/8 channel groups,
+// 256/(C/8) pixel lanes per CTA.
+struct Lanes {
+  int c8, lanes, cg, pl;
+  __device__ Lanes(int C) {
+    c8 = C >> 3;
+    lanes = kBnThreads / c8;
+    cg = threadIdx.x % c8;
+    pl = threadIdx.x / c8;
+  }
+};
+
+// Block-level fold of per-thread (a[8], b[8]) over pixel lanes -> partial[chunk][2][C].
+__device__ __forceinline__ void fold_to_partial(const Lanes& L, float (&a)[8], float (&b)[8], float* smem,
+                                                float* partial, int C) {
+  // smem layout: [lanes][2][C]
+  if (L.pl < L.lanes) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      smem[(L.pl * 2 + 0) * C + L.cg * 8 + i] = a[i];
+      smem[(L.pl * 2 + 1) * C + L.cg * 8 + i] = b[i];
+    }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 2 * C; idx += kBnThreads) {
+    float s = 0.f;
+    for (int l = 0; l < L.lanes; ++l) s += smem[l * 2 * C + idx];
+    partial[(size_t)blockIdx.x * 2 * C + idx] = s;
+  }
+}
+
+__device__ __forceinline__ bool take_ticket_last(unsigned int* ticket) {
+  __shared__ unsigned int s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int old = atomicAdd(ticket, 1u);
+    s_last = (old == gridDim.x - 1) ? 1u : 0u;
+    if (s_last) *ticket = 0;
+  }
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last != 0;
+}
+
+// ------------------------------------------------------------------ forward stats
+__global__ void __launch_bounds__(kBnThreads)
+bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* __restrict__ partial, unsigned int* ticket, int M, int C,
+                int rows_per_chunk, const float* __restrict__ gamma, const float* __restrict__ beta,
+                float* running_mean, float* running_var, long long* nbt, float* save_mean, float* save_invstd,
+                float* scale, float* shift, float eps, float momentum) {
+  extern __shared__ float smem[];
+  Lanes L(C);
+  float s[8], q[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
+  const int r0 = blockIdx.x * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
+  if (L.pl < L.lanes) {
+    for (int r = r0 + L.pl; r < r1; r += L.lanes) {
+      const uint4 u = *reinterpret_cast<const uint4*>(y + (size_t)r * C + L.cg * 8);
+      float f[8];
+      bf16x8_to_float(u, f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] += f[i] * f[i]; }
+    }
+  }
+  fold_to_partial(L, s, q, smem, partial, C);
+  if (!take_ticket_last(ticket)) return;
+  // ---- last CTA: finalize ----
+  const float inv_m = 1.f / (float)M;
+  for (int c = threadIdx.x; c < C; c += kBnThreads) {
+    float sum = 0.f, sq = 0.f;
+    for (int k = 0; k < (int)gridDim.x; ++k) {
+      sum += __ldcg(&partial[(size_t)k * 2 * C + c]);
+      sq += __ldcg(&partial[(size_t)k * 2 * C + C + c]);
+    }
+    const float mean = sum * inv_m;
+    const float var = fmaxf(sq * inv_m - mean * mean, 0.f);
+    const float invstd = rsqrtf(var + eps);
+    save_mean[c] = mean;
+    save_invstd[c] = invstd;
+    const float g = gamma[c];
+    scale[c] = g * invstd;
+    shift[c] = beta[c] - mean * g * invstd;
+    const float unbiased = (M > 1) ? var * (float)M / (float)(M - 1) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+  }
+  if (threadIdx.x == 0 && nbt) *nbt += 1;
+}
+
+__global__ void bn_eval_coeffs_kernel(const float* gamma, const float* beta, const float* rm, const float* rv,
+                                      float* scale, float* shift, int C, float eps) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) {
+    const float is = rsqrtf(rv[c] + eps);
+    scale[c] = gamma[c] * is;
+    shift[c] = beta[c] - rm[c] * gamma[c] * is;
+  }
+}
+
+// ------------------------------------------------------------------ forward apply
+__global__ void __launch_bounds__(256)
+bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
+                const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out, long long total8, int C,
+                int relu) {
+  const int c8 = C >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total8;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c8);
+    const uint4 u = reinterpret_cast<const uint4*>(y)[i];
+    float f[8];
+    bf16x8_to_float(u, f);
+    const float4 s0 = reinterpret_cast<const float4*>(scale)[cg * 2], s1 = reinterpret_cast<const float4*>(scale)[cg * 2 + 1];
+    const float4 h0 = reinterpret_cast<const float4*>(shift)[cg * 2], h1 = reinterpret_cast<const float4*>(shift)[cg * 2 + 1];
+    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = f[k] * sc[k] + sh[k];
+    if (res) {
+      float r[8];
+      bf16x8_to_float(reinterpret_cast<const uint4*>(res)[i], r);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] += r[k];
+    }
+    if (relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+    }
+    reinterpret_cast<uint4*>(out)[i] = float_to_bf16x8(f);
+  }
+}
+
+// ------------------------------------------------------------------ backward reduce
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
+                     const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+                     const float* __restrict__ invstd, float* __restrict__ partial, unsigned int* ticket, int M, int C,
+                     int rows_per_chunk, int relu, float* dgamma, float* dbeta) {
+  extern __shared__ float smem[];
+  Lanes L(C);
+  float a[8], b[8], mu[8], is[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { a[i] = 0.f; b[i] = 0.f; }
+  if (L.pl < L.lanes) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { mu[i] = mean[L.cg * 8 + i]; is[i] = invstd[L.cg * 8 + i]; }
+    const int r0 = blockIdx.x * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
+    for (int r = r0 + L.pl; r < r1; r += L.lanes) {
+      const size_t off = (size_t)r * C + L.cg * 8;
+      float g[8], yy[8];
+      bf16x8_to_float(*reinterpret_cast<const uint4*>(dout + off), g);
+      bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), yy);
+      if (relu) {
+        float o[8];
+        bf16x8_to_float(*reinterpret_cast<const uint4*>(outp + off), o);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) g[i] = (o[i] > 0.f) ? g[i] : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { a[i] += g[i]; b[i] += g[i] * (yy[i] - mu[i]) * is[i]; }
+    }
+  }
+  fold_to_partial(L, a, b, smem, partial, C);
+  if (!take_ticket_last(ticket)) return;
+  for (int c = threadIdx.x; c < C; c += kBnThreads) {
+    float sa = 0.f, sb = 0.f;
+    for (int k = 0; k < (int)gridDim.x; ++k) {
+      sa += __ldcg(&partial[(size_t)k * 2 * C + c]);
+      sb += __ldcg(&partial[(size_t)k * 2 * C + C + c]);
+    }
+    dbeta[c] = sa;
+    dgamma[c] = sb;
+  }
+}
+
+// ------------------------------------------------------------------ backward apply
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
+                    const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+                    const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    const float* __restrict__ dgamma, const float* __restrict__ dbeta,
+                    __nv_bfloat16* __restrict__ dy_raw, __nv_bfloat16* __restrict__ dres, long long total8, int C,
+                    int relu, int res_accumulate, float inv_m) {
+  const int c8 = C >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total8;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % c8) * 8;
+    float g[8], yy[8];
+    bf16x8_to_float(reinterpret_cast<const uint4*>(dout)[i], g);
+    bf16x8_to_float(reinterpret_cast<const uint4*>(y)[i], yy);
+    if (relu) {
+      float o[8];
+      bf16x8_to_float(reinterpret_cast<const uint4*>(outp)[i], o);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = (o[k] > 0.f) ? g[k] : 0.f;
+    }
+    if (dres) {
+      if (res_accumulate) {
+        float r[8];
+        bf16x8_to_float(reinterpret_cast<const uint4*>(dres)[i], r);
+        float t[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t[k] = r[k] + g[k];
+        reinterpret_cast<uint4*>(dres)[i] = float_to_bf16x8(t);
+      } else {
+        reinterpret_cast<uint4*>(dres)[i] = float_to_bf16x8(g);
+      }
+    }
+    float o8[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c0 + k;
+      const float is = invstd[c];
+      const float xh = (yy[k] - mean[c]) * is;
+      o8[k] = gamma[c] * is * (g[k] - dbeta[c] * inv_m - xh * dgamma[c] * inv_m);
+    }
+    reinterpret_cast<uint4*>(dy_raw)[i] = float_to_bf16x8(o8);
+  }
+}
+
+// ------------------------------------------------------------------ stem im2col (fp32 NCHW -> bf16 rows)
+__global__ void __launch_bounds__(256)
+im2col_stem_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col, int N, int C, int H, int W, int R,
+                   int stride, int pad, int P, int Q, int Kpad) {
+  // one thread per (pixel, 8 consecutive k)
+  const int k8 = Kpad >> 3;
+  const long long total = (long long)N * P * Q * k8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int kg = (int)(i % k8);
+    const long long pix = i / k8;
+    const int q = (int)(pix % Q), pp = (int)((pix / Q) % P), n = (int)(pix / ((long long)P * Q));
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = kg * 8 + j;
+      float v = 0.f;
+      if (k < R * R * C) {
+        const int c = k % C, tap = k / C, r = tap / R, s = tap % R;
+        const int h = pp * stride - pad + r, w = q * stride - pad + s;
+        if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((size_t)n * C + c) * H + h) * W + w];
+      }
+      f[j] = v;
+    }
+    reinterpret_cast<uint4*>(col)[i] = float_to_bf16x8(f);
+  }
+}
+
+// ------------------------------------------------------------------ max pool NHWC bf16
+__global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int H,
+                                   int W, int C, int k, int stride, int pad, int P, int Q) {
+  const int c8 = C >> 3;
+  const long long total = (long long)N * P * Q * c8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c8);
+    const long long pix = i / c8;
+    const int q = (int)(pix % Q), p = (int)((pix / Q) % P), n = (int)(pix / ((long long)P * Q));
+    float m[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+    for (int r = 0; r < k; ++r)
+      for (int s = 0; s < k; ++s) {
+        const int h = p * stride - pad + r, w = q * stride - pad + s;
+        if (h < 0 || h >= H || w < 0 || w >= W) continue;
+        float f[8];
+        bf16x8_to_float(*reinterpret_cast<const uint4*>(x + (((size_t)n * H + h) * W + w) * C + cg * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], f[j]);
+      }
+    reinterpret_cast<uint4*>(y)[i] = float_to_bf16x8(m);
+  }
+}
+
+// dx[h,w] = sum over windows containing (h,w) whose max equals x[h,w] (first-match tie-break as torch)
+__global__ void maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
+                                   const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int H,
+                                   int W, int C, int k, int stride, int pad, int P, int Q) {
+  const int c8 = C >> 3;
+  const long long total = (long long)N * H * W * c8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c8);
+    const long long pix = i / c8;
+    const int w = (int)(pix % W), h = (int)((pix / W) % H), n = (int)(pix / ((long long)H * W));
+    float xv[8], acc[8];
+    bf16x8_to_float(reinterpret_cast<const uint4*>(x)[i], xv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int p = max(0, (h + pad - k + stride) / stride); p <= min(P - 1, (h + pad) / stride); ++p)
+      for (int q = max(0, (w + pad - k + stride) / stride); q <= min(Q - 1, (w + pad) / stride); ++q) {
+        const size_t o = (((size_t)n * P + p) * Q + q) * C + cg * 8;
+        float yv[8], gv[8];
+        bf16x8_to_float(*reinterpret_cast<const uint4*>(y + o), yv);
+        bf16x8_to_float(*reinterpret_cast<const uint4*>(dy + o), gv);
+        // first-match: (h,w) must be the first window element (row-major) equal to the max
+        for (int j = 0; j < 8; ++j) {
+          if (xv[j] != yv[j]) continue;
+          bool first = true;
+          for (int r = 0; r < k && first; ++r)
+            for (int s = 0; s < k; ++s) {
+              const int hh = p * stride - pad + r, ww = q * stride - pad + s;
+              if (hh == h && ww == w) { r = k; break; }
+              if (hh < 0 || hh >= H || ww < 0 || ww >= W) continue;
+              if (__bfloat162float(x[(((size_t)n * H + hh) * W + ww) * C + cg * 8 + j]) == yv[j]) { first = false; break; }
+            }
+          if (first) acc[j] += gv[j];
+        }
+      }
+    reinterpret_cast<uint4*>(dx)[i] = float_to_bf16x8(acc);
+  }
+}
+
+static int grid_for(long long work, int threads, int max_blocks = 148 * 8) {
+  long long b = (work + threads - 1) / threads;
+  return (int)std::max(1LL, std::min<long long>(b, max_blocks));
+}
+
+}  // namespace ldnn
+
+using namespace ldnn;
+#define COUNT_LAUNCH() g_launches.fetch_add(1, std::memory_order_relaxed)
+
+extern "C" int ldnn_bn_fwd_stats(const void* y, int M, int C, int chunks, float* partial, unsigned int* ticket,
+                                 const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                 long long* nbt, float* save_mean, float* save_invstd, float* scale, float* shift,
+                                 float eps, float momentum, void* stream) {
+  LDNN_ARG(C % 8 == 0 && C / 8 <= kBnThreads, "bn: C=%d unsupported (need C%%8==0, C<=2048)", C);
+  LDNN_ARG(chunks >= 1, "bn: chunks");
+  const int rows = (M + chunks - 1) / chunks;
+  const int lanes = kBnThreads / (C / 8);
+  const size_t smem = (size_t)lanes * 2 * C * sizeof(float);
+  bn_stats_kernel<<<chunks, kBnThreads, smem, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)y, partial, ticket, M, C, rows, gamma, beta, running_mean, running_var, nbt, save_mean,
+      save_invstd, scale, shift, eps, momentum);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_bn_eval_coeffs(const float* gamma, const float* beta, const float* rm, const float* rv,
+                                   float* scale, float* shift, int C, float eps, void* stream) {
+  bn_eval_coeffs_kernel<<<(C + 255) / 256, 256, 0, (cudaStream_t)stream>>>(gamma, beta, rm, rv, scale, shift, C, eps);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_bn_fwd_apply(const void* y, const float* scale, const float* shift, const void* residual,
+                                 void* out, int M, int C, int relu, void* stream) {
+  LDNN_ARG(C % 8 == 0, "bn: C %% 8");
+  const long long total8 = (long long)M * C / 8;
+  bn_apply_kernel<<<grid_for(total8, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)y, scale, shift, (const __nv_bfloat16*)residual, (__nv_bfloat16*)out, total8, C, relu);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_bn_bwd_reduce(const void* dout, const void* out, const void* y, const float* save_mean,
+                                  const float* save_invstd, float* partial, unsigned int* ticket, int M, int C,
+                                  int chunks, int relu, float* dgamma, float* dbeta, void* stream) {
+  LDNN_ARG(C % 8 == 0 && C / 8 <= kBnThreads, "bn: C=%d unsupported", C);
+  const int rows = (M + chunks - 1) / chunks;
+  const int lanes = kBnThreads / (C / 8);
+  const size_t smem = (size_t)lanes * 2 * C * sizeof(float);
+  bn_bwd_reduce_kernel<<<chunks, kBnThreads, smem, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, partial,
+      ticket, M, C, rows, relu, dgamma, dbeta);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_bn_bwd_apply(const void* dout, const void* out, const void* y, const float* save_mean,
+                                 const float* save_invstd, const float* gamma, const float* dgamma,
+                                 const float* dbeta, void* dy_raw, void* dres, int M, int C, int relu,
+                                 int res_accumulate, void* stream) {
+  const long long total8 = (long long)M * C / 8;
+  bn_bwd_apply_kernel<<<grid_for(total8, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, gamma,
+      dgamma, dbeta, (__nv_bfloat16*)dy_raw, (__nv_bfloat16*)dres, total8, C, relu, res_accumulate, 1.f / (float)M);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_im2col_stem(const float* x, void* col, int N, int C, int H, int W, int R, int stride, int pad,
+                                int Kpad, void* stream) {
+  LDNN_ARG(Kpad % 64 == 0 && Kpad >= R * R * C, "im2col: Kpad=%d", Kpad);
+  const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - R) / stride + 1;
+  const long long total = (long long)N * P * Q * (Kpad / 8);
+  im2col_stem_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)col, N, C, H, W, R,
+                                                                           stride, pad, P, Q, Kpad);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_maxpool_fwd(const void* x, void* y, int N, int H, int W, int C, int k, int stride, int pad,
+                                void* stream) {
+  const int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
+  const long long total = (long long)N * P * Q * (C / 8);
+  maxpool_fwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C, k, stride, pad, P, Q);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C,
+                                int k, int stride, int pad, void* stream) {
+  const int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
+  const long long total = (long long)N * H * W * (C / 8);
+  maxpool_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, k,
+      stride, pad, P, Q);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}

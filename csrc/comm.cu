@@ -1,0 +1,446 @@
+// Symmetric memory + the fused peer-to-peer exchange kernels (K-AR, K-RING, K-DRING, K-BCAST,
+// K-BAR, K-MET).
+//
+// The reference exchanges gradients/weights once per global epoch, one tensor at a time, through
+// torch.distributed all_reduce + a separate scale kernel (Balanced All-Reduce/communication.py:4-31)
+// or through host-staged mpi4py Isend/Irecv + numpy round trips (Balanced Ring/communication.py:5-62,
+// Balanced Double-Ring/communication.py:5-77).  Here every topology is ONE kernel over a flat fp32
+// slab that loads/stores directly into the peers' buffers over NVLink/NVSwitch:
+//   * system-scope release/acquire flags in a peer-mapped signal pad (never reset: the value is a
+//     strictly increasing epoch, so there is no ABA across calls),
+//   * 16-byte relaxed.sys vector loads/stores for the payload, reduction in fp32 registers,
+//   * the per-rank weight (1/ws, n_r/sum n, or the local_weight forms), the Adam/SGD update and
+//     the bf16 cast of the updated parameters run in the same pass (optim.cuh),
+//   * every spin-wait carries a watchdog.
+// `emulate=1` plays all ranks in one cooperative launch on one GPU (blockIdx.y = rank) so the
+// exact kernel code is testable without multiple devices.
+#include "../include/ldnn_b200.h"
+#include "common.cuh"
+#include "optim.cuh"
+#include <atomic>
+#include <cooperative_groups.h>
+
+namespace ldnn {
+extern std::atomic<unsigned long long> g_launches;
+
+constexpr int kCommThreads = 512;
+constexpr int kBarWords = 512 * LDNN_MAX_RANKS;        // barrier slots: [block][src rank]
+constexpr int kFlagWords = LDNN_SIGNAL_WORDS - kBarWords;
+
+struct Peers { void* p[LDNN_MAX_RANKS]; };
+
+// ------------------------------------------------------------------ system-scope primitives
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_sys_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_sys_f4(float4* p, const float4& v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+struct Ctx {
+  int rank, world, block, blocks;
+  unsigned long long timeout;
+  int* err;
+  unsigned int* sig[LDNN_MAX_RANKS];
+};
+
+__device__ __forceinline__ Ctx make_ctx(const ldnn_comm& c) {
+  Ctx x;
+  x.rank = c.emulate ? (int)blockIdx.y : c.rank;
+  x.world = c.world;
+  x.block = blockIdx.x;
+  x.blocks = gridDim.x;
+  x.timeout = c.timeout_cycles ? c.timeout_cycles : (1ull << 35);
+  x.err = c.error_flag;
+#pragma unroll
+  for (int i = 0; i < LDNN_MAX_RANKS; ++i) x.sig[i] = reinterpret_cast<unsigned int*>(c.signal[i]);
+  return x;
+}
+
+// Wait until *p has reached `seq` (wrap-safe).  Returns false on watchdog expiry.
+__device__ __forceinline__ bool spin_until(const Ctx& x, const unsigned int* p, unsigned int seq) {
+  const long long t0 = clock64();
+  while ((int)(ld_acquire_sys(p) - seq) < 0) {
+    if ((unsigned long long)(clock64() - t0) > x.timeout) {
+      if (x.err) atomicExch(x.err, 1);
+      return false;
+    }
+    __nanosleep(40);
+  }
+  return true;
+}
+
+// K-BAR: CTA `block` of every rank meets.  Release: all of this CTA's earlier writes (incl. peer
+// stores) are visible to whoever observes the flag; acquire: symmetric.
+__device__ __forceinline__ void comm_barrier(const Ctx& x, unsigned int seq) {
+  __syncthreads();
+  if ((int)threadIdx.x < x.world) {
+    __threadfence_system();
+    st_release_sys(x.sig[threadIdx.x] + x.block * LDNN_MAX_RANKS + x.rank, seq);
+    spin_until(x, x.sig[x.rank] + x.block * LDNN_MAX_RANKS + threadIdx.x, seq);
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 f4_scale(const float4& a, float s) { return make_float4(a.x * s, a.y * s, a.z * s, a.w * s); }
+__device__ __forceinline__ float4 f4_fma(const float4& a, float s, const float4& b) {
+  return make_float4(fmaf(a.x, s, b.x), fmaf(a.y, s, b.y), fmaf(a.z, s, b.z), fmaf(a.w, s, b.w));
+}
+
+// ================================================================== K-AR: two-shot all-reduce
+__global__ void __launch_bounds__(kCommThreads, 1)
+allreduce_fused_kernel(const ldnn_comm c, const ldnn_exchange e) {
+  const Ctx x = make_ctx(c);
+  const int W = x.world, r = x.rank;
+  const long long n4 = e.n >> 2;
+  const long long per = (n4 + W - 1) / W;
+  const long long lo = min((long long)r * per, n4), hi = min(lo + per, n4);
+  const unsigned int seq = c.epoch * 4u;
+  const bool update = (e.mode & LDNN_X_UPDATE) != 0, selfmix = (e.mode & LDNN_X_SELFMIX) != 0;
+
+  comm_barrier(x, seq + 1);   // every rank's input slab is final
+
+  float4* const my_params = reinterpret_cast<float4*>(e.params[r]);
+  float4* const my_m = reinterpret_cast<float4*>(e.m);
+  float4* const my_v = reinterpret_cast<float4*>(e.v);
+  const long long stride = (long long)x.blocks * kCommThreads;
+  for (long long i = lo + (long long)x.block * kCommThreads + threadIdx.x; i < hi; i += 2 * stride) {
+    const long long i1 = i + stride;
+    const bool two = i1 < hi;
+    float4 a0[LDNN_MAX_RANKS], a1[LDNN_MAX_RANKS];
+#pragma unroll
+    for (int p = 0; p < LDNN_MAX_RANKS; ++p) {
+      if (p < W) {
+        const float4* src = reinterpret_cast<const float4*>(e.grads[p]);
+        a0[p] = ld_sys_f4(src + i);
+        if (two) a1[p] = ld_sys_f4(src + i1);
+      }
+    }
+    float4 s0 = make_float4(0, 0, 0, 0), s1 = s0;
+#pragma unroll
+    for (int p = 0; p < LDNN_MAX_RANKS; ++p) {
+      if (p < W) { s0 = f4_fma(a0[p], e.weight[p], s0); if (two) s1 = f4_fma(a1[p], e.weight[p], s1); }
+    }
+    if (update && !selfmix) {
+      // fused tail: optimizer on the owned slice, then push the *updated parameters*
+      float4 p0 = my_params[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
+      optim_update4(p0, s0, m0, v0, e.opt);
+      my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
+      s0 = p0;
+      if (two) {
+        float4 p1 = my_params[i1], m1 = my_m[i1], v1 = e.opt.kind == 0 ? my_v[i1] : make_float4(0, 0, 0, 0);
+        optim_update4(p1, s1, m1, v1, e.opt);
+        my_m[i1] = m1; if (e.opt.kind == 0) my_v[i1] = v1;
+        s1 = p1;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < LDNN_MAX_RANKS; ++q) {
+      if (q < W) {
+        float4* dst = reinterpret_cast<float4*>(selfmix ? e.recv[q] : (update ? e.params[q] : e.grads[q]));
+        st_sys_f4(dst + i, s0);
+        if (two) st_sys_f4(dst + i1, s1);
+      }
+    }
+  }
+
+  comm_barrier(x, seq + 2);   // all pushes have landed everywhere
+
+  // ---- local pass over the whole slab: self-mix, (per-rank) update, bf16 cast ----
+  const bool cast = e.shadow != nullptr && (update || (e.mode & 4));
+  if (selfmix || cast) {
+    float4* g = reinterpret_cast<float4*>(e.grads[r]);
+    const float4* rv = reinterpret_cast<const float4*>(e.recv[r]);
+    __nv_bfloat16* sh = reinterpret_cast<__nv_bfloat16*>(e.shadow);
+    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n4; i += stride) {
+      float4 val;
+      if (selfmix) {
+        val = f4_fma(g[i], e.self_coef, rv[i]);
+        if (update) {
+          float4 p0 = my_params[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
+          optim_update4(p0, val, m0, v0, e.opt);
+          my_params[i] = p0; my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
+          val = p0;
+        } else {
+          g[i] = val;
+        }
+      } else {
+        val = update ? my_params[i] : g[i];
+      }
+      if (cast) store_bf16x4(sh + 4 * i, val);
+    }
+  }
+}
+
+// ================================================================== K-RING / K-DRING: RS + AG rings
+// Region k of the slab belongs to ring k; ring 0 rotates +1 (pull from r-1), ring 1 rotates -1.
+// Flags: sig[kBarWords + ((ring*J + j) * 16 + step)] on the *producer's* pad (readers poll the
+// producer's pad through the peer mapping).
+__global__ void __launch_bounds__(kCommThreads, 1)
+ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings, const int J, const long long sub4) {
+  const Ctx x = make_ctx(c);
+  const int W = x.world, r = x.rank;
+  const long long n4 = e.n >> 2;
+  const unsigned int seq = c.epoch * 4u;
+  const bool update = (e.mode & LDNN_X_UPDATE) != 0;
+  const bool cast = e.shadow != nullptr && (update || (e.mode & 4));
+
+  comm_barrier(x, seq + 1);
+
+  const int blocks_per_ring = x.blocks / num_rings;
+  const int ring = min(x.block / blocks_per_ring, num_rings - 1);
+  const int bir = x.block - ring * blocks_per_ring;
+  const int dir = (ring == 0) ? 1 : -1;
+  const int prev = (r - dir + W) % W;
+  const long long reg_lo = n4 * ring / num_rings, reg_hi = n4 * (ring + 1) / num_rings;
+  const long long chunk4 = (reg_hi - reg_lo + W - 1) / W;
+
+  float4* const gr = reinterpret_cast<float4*>(e.grads[r]);
+  const float4* const gp = reinterpret_cast<const float4*>(e.grads[prev]);
+  float4* const pr = reinterpret_cast<float4*>(e.params[r]);
+  const float4* const pp = reinterpret_cast<const float4*>(e.params[prev]);
+  float4* const my_m = reinterpret_cast<float4*>(e.m);
+  float4* const my_v = reinterpret_cast<float4*>(e.v);
+  __nv_bfloat16* const sh = reinterpret_cast<__nv_bfloat16*>(e.shadow);
+  unsigned int* const my_flags = x.sig[r] + kBarWords;
+  const unsigned int* const prev_flags = x.sig[prev] + kBarWords;
+  const int nsteps = 2 * (W - 1);
+  bool alive = true;
+
+  for (int step = 0; step < nsteps && W > 1; ++step) {
+    const bool rs = step < W - 1;
+    const int s = rs ? step : step - (W - 1);
+    // chunk handled at this step
+    int cidx = rs ? (r - dir * (1 + s)) : (r - dir * s);
+    cidx = ((cidx % W) + W) % W;
+    const long long c_lo = min(reg_lo + (long long)cidx * chunk4, reg_hi), c_hi = min(c_lo + chunk4, reg_hi);
+    const bool last_rs = rs && (s == W - 2);
+    for (int j = bir; j < J; j += blocks_per_ring) {
+      const long long lo = min(c_lo + (long long)j * sub4, c_hi), hi = min(lo + sub4, c_hi);
+      const int fidx = (ring * J + j) * 16;
+      if (step > 0) {
+        if (threadIdx.x == 0 && alive) alive = spin_until(x, prev_flags + fidx + (step - 1), seq + 2);
+        __syncthreads();
+      }
+      if (rs) {
+        for (long long i = lo + threadIdx.x; i < hi; i += kCommThreads) {
+          float4 in = ld_sys_f4(gp + i);
+          if (s == 0) in = f4_scale(in, e.weight[prev]);
+          float4 acc = f4_fma(gr[i], e.weight[r], in);
+          if (last_rs && update) {
+            float4 p0 = pr[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
+            optim_update4(p0, acc, m0, v0, e.opt);
+            pr[i] = p0; my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
+            if (cast) store_bf16x4(sh + 4 * i, p0);
+          } else {
+            gr[i] = acc;
+            if (last_rs && cast) store_bf16x4(sh + 4 * i, acc);
+          }
+        }
+      } else {
+        for (long long i = lo + threadIdx.x; i < hi; i += kCommThreads) {
+          if (update) {
+            const float4 v = ld_sys_f4(pp + i);
+            pr[i] = v;
+            if (cast) store_bf16x4(sh + 4 * i, v);
+          } else {
+            const float4 v = ld_sys_f4(gp + i);
+            gr[i] = v;
+            if (cast) store_bf16x4(sh + 4 * i, v);
+          }
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        st_release_sys(my_flags + fidx + step, seq + 2);
+      }
+    }
+  }
+  if (W == 1 && (update || cast)) {
+    // single rank: plain fused optimizer / cast over the whole slab
+    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n4; i += (long long)x.blocks * kCommThreads) {
+      float4 val = f4_scale(gr[i], e.weight[0]);
+      if (update) {
+        float4 p0 = pr[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
+        optim_update4(p0, val, m0, v0, e.opt);
+        pr[i] = p0; my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
+        val = p0;
+      }
+      if (cast) store_bf16x4(sh + 4 * i, val);
+    }
+  }
+  comm_barrier(x, seq + 3);   // nobody is still pulling from a slab that is about to be reused
+}
+
+// ================================================================== compat gossip (1- or 2-hop pull)
+__global__ void __launch_bounds__(kCommThreads, 1)
+gossip_pull_kernel(const ldnn_comm c, const Peers bufs, const Peers recv, const long long n4, const float c_self,
+                   const int n_off, const int off0, const int off1, const float c0, const float c1) {
+  const Ctx x = make_ctx(c);
+  const int W = x.world, r = x.rank;
+  const unsigned int seq = c.epoch * 4u;
+  comm_barrier(x, seq + 1);
+  const float4* mine = reinterpret_cast<const float4*>(bufs.p[r]);
+  const float4* p0 = reinterpret_cast<const float4*>(bufs.p[((r - off0) % W + W) % W]);
+  const float4* p1 = reinterpret_cast<const float4*>(bufs.p[((r - off1) % W + W) % W]);
+  float4* out = reinterpret_cast<float4*>(recv.p[r]);
+  const long long stride = (long long)x.blocks * kCommThreads;
+  for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n4; i += stride) {
+    float4 acc = f4_scale(mine[i], c_self);
+    if (n_off > 0) acc = f4_fma(ld_sys_f4(p0 + i), c0, acc);
+    if (n_off > 1) acc = f4_fma(ld_sys_f4(p1 + i), c1, acc);
+    out[i] = acc;
+  }
+  comm_barrier(x, seq + 2);   // every reader is done with the old values: safe to overwrite in place
+  float4* dst = reinterpret_cast<float4*>(bufs.p[r]);
+  for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n4; i += stride) dst[i] = out[i];
+}
+
+// ================================================================== K-BCAST
+__global__ void __launch_bounds__(kCommThreads, 1)
+broadcast_kernel(const ldnn_comm c, const Peers bufs, const long long n16, const int src) {
+  const Ctx x = make_ctx(c);
+  const unsigned int seq = c.epoch * 4u;
+  comm_barrier(x, seq + 1);
+  if (x.rank != src) {
+    const float4* s = reinterpret_cast<const float4*>(bufs.p[src]);
+    float4* d = reinterpret_cast<float4*>(bufs.p[x.rank]);
+    const long long stride = (long long)x.blocks * kCommThreads;
+    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n16; i += stride) d[i] = ld_sys_f4(s + i);
+  }
+  comm_barrier(x, seq + 2);
+}
+
+// ================================================================== K-MET
+__global__ void __launch_bounds__(kCommThreads, 1)
+allgather_small_kernel(const ldnn_comm c, const float* mine, const Peers tables, const int count) {
+  const Ctx x = make_ctx(c);
+  const unsigned int seq = c.epoch * 4u;
+  const float* src = c.emulate ? mine + (size_t)x.rank * count : mine;
+  comm_barrier(x, seq + 1);
+  if (x.block == 0)
+    for (int q = 0; q < x.world; ++q)
+      for (int i = threadIdx.x; i < count; i += kCommThreads)
+        reinterpret_cast<float*>(tables.p[q])[(size_t)x.rank * count + i] = src[i];
+  comm_barrier(x, seq + 2);
+}
+
+__global__ void __launch_bounds__(kCommThreads, 1) barrier_kernel(const ldnn_comm c) {
+  const Ctx x = make_ctx(c);
+  comm_barrier(x, c.epoch * 4u + 1);
+}
+
+// ------------------------------------------------------------------ launch helper
+template <typename... Args>
+static int launch_comm(void (*kernel)(Args...), const ldnn_comm& c, cudaStream_t st, Args... args) {
+  LDNN_ARG(c.world >= 1 && c.world <= LDNN_MAX_RANKS, "world=%d", c.world);
+  LDNN_ARG(c.blocks >= 1 && c.blocks <= 512, "blocks=%d", c.blocks);
+  dim3 grid(c.blocks, c.emulate ? c.world : 1);
+  if (c.emulate) {
+    void* params[] = {(void*)&args...};
+    LDNN_CUDA(cudaLaunchCooperativeKernel((void*)kernel, grid, dim3(kCommThreads), params, 0, st));
+  } else {
+    kernel<<<grid, kCommThreads, 0, st>>>(args...);
+    LDNN_CUDA(cudaGetLastError());
+  }
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return LDNN_OK;
+}
+
+}  // namespace ldnn
+
+using namespace ldnn;
+
+// ------------------------------------------------------------------ symmetric memory (CUDA IPC)
+extern "C" int ldnn_symm_alloc(size_t bytes, void** ptr, unsigned char* handle_out) {
+  LDNN_CUDA(cudaMalloc(ptr, bytes));
+  LDNN_CUDA(cudaMemset(*ptr, 0, bytes));
+  if (handle_out) {
+    cudaIpcMemHandle_t h;
+    LDNN_CUDA(cudaIpcGetMemHandle(&h, *ptr));
+    static_assert(sizeof(h) == LDNN_IPC_HANDLE_BYTES, "ipc handle size");
+    memcpy(handle_out, &h, sizeof(h));
+  }
+  return LDNN_OK;
+}
+extern "C" int ldnn_symm_open(const unsigned char* handle, void** peer_ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  LDNN_CUDA(cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return LDNN_OK;
+}
+extern "C" int ldnn_symm_close(void* peer_ptr) { LDNN_CUDA(cudaIpcCloseMemHandle(peer_ptr)); return LDNN_OK; }
+extern "C" int ldnn_symm_free(void* ptr) { LDNN_CUDA(cudaFree(ptr)); return LDNN_OK; }
+extern "C" int ldnn_enable_peer_access(int my_device, int peer_device) {
+  int can = 0;
+  LDNN_CUDA(cudaDeviceCanAccessPeer(&can, my_device, peer_device));
+  LDNN_ARG(can, "device %d cannot access peer %d", my_device, peer_device);
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return LDNN_OK; }
+  LDNN_CUDA(e);
+  return LDNN_OK;
+}
+
+// ------------------------------------------------------------------ exchange entry points
+extern "C" int ldnn_allreduce_fused(const ldnn_comm* c, const ldnn_exchange* x, void* stream) {
+  LDNN_ARG(x->n % 4 == 0, "allreduce: n=%lld must be a multiple of 4", x->n);
+  LDNN_ARG(!(x->mode & LDNN_X_UPDATE) || (x->m && (x->opt.kind == 1 || x->v)), "allreduce: UPDATE needs m (and v)");
+  return launch_comm(allreduce_fused_kernel, *c, (cudaStream_t)stream, *c, *x);
+}
+
+extern "C" int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int num_rings, void* stream) {
+  LDNN_ARG(x->n % 4 == 0, "ring: n %% 4");
+  LDNN_ARG(num_rings == 1 || num_rings == 2, "ring: num_rings=%d", num_rings);
+  LDNN_ARG(!(x->mode & LDNN_X_SELFMIX), "ring: self-weighted mixing is only available on the all-reduce schedule");
+  LDNN_ARG(c->blocks >= num_rings, "ring: need >= %d blocks", num_rings);
+  const long long n4 = x->n / 4;
+  const long long chunk4 = (n4 / num_rings + c->world) / c->world + 1;
+  // sub-chunks: aim for 128 KB, cap the flag table
+  long long sub4 = 8192;
+  int J = (int)((chunk4 + sub4 - 1) / sub4);
+  const int maxJ = kFlagWords / (16 * 2);
+  if (J > maxJ) { J = maxJ; sub4 = (chunk4 + J - 1) / J; }
+  if (J < 1) J = 1;
+  return launch_comm(ring_fused_kernel, *c, (cudaStream_t)stream, *c, *x, num_rings, J, sub4);
+}
+
+extern "C" int ldnn_gossip_pull(const ldnn_comm* c, void* const* bufs, void* const* recv, long long n, float c_self,
+                                int n_off, const int* offsets, const float* coefs, void* stream) {
+  LDNN_ARG(n % 4 == 0 && n_off >= 0 && n_off <= 2, "gossip: n=%lld n_off=%d", n, n_off);
+  Peers b, r;
+  for (int i = 0; i < LDNN_MAX_RANKS; ++i) { b.p[i] = i < c->world ? bufs[i] : nullptr; r.p[i] = i < c->world ? recv[i] : nullptr; }
+  return launch_comm(gossip_pull_kernel, *c, (cudaStream_t)stream, *c, b, r, n / 4, c_self, n_off,
+                     n_off > 0 ? offsets[0] : 0, n_off > 1 ? offsets[1] : 0, n_off > 0 ? coefs[0] : 0.f,
+                     n_off > 1 ? coefs[1] : 0.f);
+}
+
+extern "C" int ldnn_broadcast(const ldnn_comm* c, void* const* bufs, size_t bytes, int src, void* stream) {
+  LDNN_ARG(bytes % 16 == 0, "broadcast: bytes %% 16");
+  Peers b;
+  for (int i = 0; i < LDNN_MAX_RANKS; ++i) b.p[i] = i < c->world ? bufs[i] : nullptr;
+  return launch_comm(broadcast_kernel, *c, (cudaStream_t)stream, *c, b, (long long)(bytes / 16), src);
+}
+
+extern "C" int ldnn_allgather_small(const ldnn_comm* c, const float* mine, void* const* tables, int count,
+                                    void* stream) {
+  Peers t;
+  for (int i = 0; i < LDNN_MAX_RANKS; ++i) t.p[i] = i < c->world ? tables[i] : nullptr;
+  return launch_comm(allgather_small_kernel, *c, (cudaStream_t)stream, *c, mine, t, count);
+}
+
+extern "C" int ldnn_barrier(const ldnn_comm* c, void* stream) {
+  return launch_comm(barrier_kernel, *c, (cudaStream_t)stream, *c);
+}

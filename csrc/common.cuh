@@ -1,0 +1,56 @@
+// Shared host/device helpers for libldnn_b200.
+#pragma once
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+
+#define LDNN_OK 0
+#define LDNN_ERR_CUDA 1
+#define LDNN_ERR_ARG 2
+#define LDNN_ERR_TIMEOUT 3
+
+namespace ldnn {
+
+void set_last_error(const char* fmt, ...);
+
+#define LDNN_CUDA(expr)                                                                  \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      ::ldnn::set_last_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return LDNN_ERR_CUDA;                                                              \
+    }                                                                                    \
+  } while (0)
+
+#define LDNN_ARG(cond, ...)                      \
+  do {                                           \
+    if (!(cond)) {                               \
+      ::ldnn::set_last_error(__VA_ARGS__);       \
+      return LDNN_ERR_ARG;                       \
+    }                                            \
+  } while (0)
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void bf16x8_to_float(const uint4& u, float (&f)[8]) {
+  const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(b[i]);
+    f[2 * i] = t.x; f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 float_to_bf16x8(const float (&f)[8]) {
+  uint4 u;
+  __nv_bfloat162* b = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) b[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return u;
+}
+
+}  // namespace ldnn

@@ -1,0 +1,346 @@
+// Host side of the implicit-GEMM convolution: tensor-map construction, tiling / split-K
+// heuristics, launch plans.  Kernel: conv_gemm.cuh.
+#include <cstdarg>
+#include <cstring>
+#include <vector>
+#include <mutex>
+#include <atomic>
+
+#include "../include/ldnn_b200.h"
+#include "common.cuh"
+#include "conv_gemm.cuh"
+
+namespace ldnn {
+
+static thread_local char g_err[512] = "";
+std::atomic<unsigned long long> g_launches{0};
+
+void set_last_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+// ---- cuTensorMapEncodeTiled through the runtime (no link-time libcuda dependency) ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// bf16 tensor, up to 4 dims, innermost contiguous, 128B swizzle, zero OOB fill.
+static int make_map(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_elems,
+                    const uint32_t* box) {
+  EncodeTiledFn enc = get_encode();
+  LDNN_ARG(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t gdim[4], gstr[3];
+  cuuint32_t bx[4], es[4];
+  for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 1; i < rank; ++i) gstr[i - 1] = strides_elems[i] * 2;
+  LDNN_ARG((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16-byte aligned", base);
+  for (int i = 0; i < rank - 1; ++i) LDNN_ARG(gstr[i] % 16 == 0, "TMA stride %d = %llu B not a multiple of 16", i,
+                                              (unsigned long long)gstr[i]);
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstr, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  LDNN_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rank %d dims %llu %llu box %u %u)", (int)r, rank,
+           (unsigned long long)gdim[0], (unsigned long long)gdim[1], bx[0], bx[1]);
+  return LDNN_OK;
+}
+
+static int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+static int cdiv(int a, int b) { return (a + b - 1) / b; }
+static int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+static int posmod(int a, int b) { int m = a % b; return m < 0 ? m + b : m; }
+
+struct Launch {
+  ConvMaps maps;
+  ConvParams p;
+  dim3 grid;
+  size_t scratch_floats = 0;   // offset bookkeeping
+  size_t ticket_off = 0, scratch_off = 0, tickets = 0;
+};
+struct Plan {
+  int mode, block_n;
+  std::vector<Launch> launches;
+  void* out;
+  const void* addend;
+  float* scratch;
+  unsigned int* tickets;
+};
+
+static void pixel_box(int Wd, int Hd, int Nd, int target, ConvParams& p) {
+  p.bw = std::min(next_pow2(Wd), target);
+  p.bh = std::min(next_pow2(Hd), target / p.bw);
+  p.bn = target / (p.bw * p.bh);
+  p.tiles_w = cdiv(Wd, p.bw);
+  p.tiles_h = cdiv(Hd, p.bh);
+  p.Wd = Wd; p.Hd = Hd; p.Nd = Nd;
+}
+
+static int pick_splits(int tiles, int iters, int requested) {
+  int s = requested;
+  if (s <= 0) {
+    s = 1;
+    if (tiles < 96) s = std::max(1, 148 / tiles);
+    s = std::min(s, std::max(1, iters / 4));   // keep >= 4 k-iterations per CTA
+    s = std::min(s, 32);
+  }
+  s = std::max(1, std::min(s, iters));
+  int per = cdiv(iters, s);
+  return cdiv(iters, per);                     // no empty split
+}
+
+// Builds every launch of a plan.  `dry` = only sizes (no tensor maps, pointers may be null).
+static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
+  LDNN_ARG(d.mode >= 0 && d.mode <= 2, "bad conv mode %d", d.mode);
+  LDNN_ARG(d.Cin % 64 == 0 && d.Cout % 64 == 0, "Cin=%d / Cout=%d must be multiples of 64", d.Cin, d.Cout);
+  LDNN_ARG(d.stride == 1 || d.stride == 2, "stride %d unsupported", d.stride);
+  LDNN_ARG(d.R * d.R <= 16, "filter %dx%d too large for the tap table", d.R, d.R);
+  const int T = d.R * d.R;
+  const int P = (d.H + 2 * d.pad - d.R) / d.stride + 1, Q = (d.W + 2 * d.pad - d.R) / d.stride + 1;
+  const int n_total = (d.mode == MODE_FPROP) ? d.Cout : d.Cin;
+  int bn_ = d.block_n;
+  if (bn_ == 0) bn_ = (n_total % 128 == 0) ? 128 : 64;
+  if (d.mode == MODE_WGRAD && d.block_n == 0) bn_ = (n_total % 256 == 0) ? 256 : ((n_total % 128 == 0) ? 128 : 64);
+  LDNN_ARG(bn_ == 64 || bn_ == 128 || bn_ == 256, "block_n %d", bn_);
+  LDNN_ARG(n_total % bn_ == 0, "N=%d not a multiple of block_n=%d", n_total, bn_);
+  plan.mode = d.mode; plan.block_n = bn_;
+  plan.out = (d.mode == MODE_FPROP) ? d.y : (d.mode == MODE_DGRAD ? const_cast<void*>(d.x) : d.dw);
+  plan.addend = d.addend ? d.addend : plan.out;
+  plan.scratch = d.scratch; plan.tickets = d.tickets;
+
+  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(d.x);
+  const __nv_bfloat16* yb = reinterpret_cast<const __nv_bfloat16*>(d.y);
+  size_t scratch_off = 0, ticket_off = 0;
+
+  // parity views of x for strided convs: view (hp,wp) has rows h = 2a+hp
+  auto x_view_map = [&](CUtensorMap* m, int hp, int wp, const uint32_t* box) -> int {
+    const int s = d.stride;
+    uint64_t dims[4] = {(uint64_t)d.Cin, (uint64_t)cdiv(d.W - wp, s), (uint64_t)cdiv(d.H - hp, s), (uint64_t)d.N};
+    uint64_t str[4] = {1, (uint64_t)s * d.Cin, (uint64_t)s * d.W * d.Cin, (uint64_t)d.H * d.W * d.Cin};
+    return make_map(m, xb + ((size_t)hp * d.W + wp) * d.Cin, 4, dims, str, box);
+  };
+  auto y_map = [&](CUtensorMap* m, const uint32_t* box) -> int {
+    uint64_t dims[4] = {(uint64_t)d.Cout, (uint64_t)Q, (uint64_t)P, (uint64_t)d.N};
+    uint64_t str[4] = {1, (uint64_t)d.Cout, (uint64_t)Q * d.Cout, (uint64_t)P * Q * d.Cout};
+    return make_map(m, yb, 4, dims, str, box);
+  };
+  auto w_map = [&](CUtensorMap* m, uint32_t box_rows) -> int {
+    uint64_t dims[2] = {(uint64_t)T * d.Cin, (uint64_t)d.Cout};
+    uint64_t str[2] = {1, (uint64_t)T * d.Cin};
+    uint32_t box[2] = {64, box_rows};
+    return make_map(m, d.w, 2, dims, str, box);
+  };
+  // forward-style tap table: input row = stride*p - pad + r
+  auto fwd_taps = [&](ConvParams& p) {
+    p.num_taps = T;
+    for (int r = 0; r < d.R; ++r)
+      for (int s = 0; s < d.R; ++s) {
+        const int th = r - d.pad, tw = s - d.pad;
+        TapEntry& te = p.taps[r * d.R + s];
+        te.map = (int8_t)(posmod(th, d.stride) * 2 + posmod(tw, d.stride));
+        if (d.stride == 1) te.map = 0;
+        te.dh = (int8_t)floordiv(th, d.stride);
+        te.dw = (int8_t)floordiv(tw, d.stride);
+        te.wtap = (int8_t)(r * d.R + s);
+      }
+  };
+  auto defaults = [&](ConvParams& p) {
+    memset(&p, 0, sizeof(p));
+    p.accumulate = d.accumulate;
+    p.n_total = n_total;
+    // K-major SW128 tile: 8-row groups 1024 B apart; MN-major: 64-wide MN blocks 8192 B apart,
+    // 8-row K groups 1024 B apart.
+    p.a_lbo = d.a_lbo ? d.a_lbo : (d.mode == MODE_WGRAD ? 8192u : 16u);
+    p.a_sbo = d.a_sbo ? d.a_sbo : 1024u;
+    p.b_lbo = d.b_lbo ? d.b_lbo : (d.mode == MODE_FPROP ? 16u : 8192u);
+    p.b_sbo = d.b_sbo ? d.b_sbo : 1024u;
+  };
+  auto finish = [&](Launch& L, int tiles_for_split) {
+    ConvParams& p = L.p;
+    p.splits = pick_splits(tiles_for_split, p.iters_total, d.splits);
+    p.iters_per_split = cdiv(p.iters_total, p.splits);
+    if (p.splits > 1) {
+      L.scratch_off = scratch_off; L.ticket_off = ticket_off;
+      scratch_off += (size_t)tiles_for_split * p.splits * 128 * bn_;
+      ticket_off += tiles_for_split;
+    }
+  };
+
+  if (d.mode == MODE_FPROP) {
+    Launch L;
+    ConvParams& p = L.p;
+    defaults(p);
+    pixel_box(Q, P, d.N, 128, p);
+    fwd_taps(p);
+    p.kb_per_tap = d.Cin / 64; p.red_ch = d.Cin;
+    p.iters_total = T * p.kb_per_tap;
+    p.out_base = 0; p.sW = d.Cout; p.sH = (long long)Q * d.Cout; p.sN = (long long)P * Q * d.Cout;
+    const int m_tiles = p.tiles_w * p.tiles_h * cdiv(d.N, p.bn), n_tiles = d.Cout / bn_;
+    finish(L, m_tiles * n_tiles);
+    L.grid = dim3(m_tiles, n_tiles, p.splits);
+    if (!dry) {
+      uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+      const int nviews = d.stride == 1 ? 1 : 4;
+      for (int v = 0; v < 4; ++v) {
+        int rc = x_view_map(&L.maps.act[v], v < nviews ? v / 2 : 0, v < nviews ? v % 2 : 0, box);
+        if (rc) return rc;
+      }
+      int rc = w_map(&L.maps.other, bn_);
+      if (rc) return rc;
+    }
+    plan.launches.push_back(L);
+  } else if (d.mode == MODE_DGRAD) {
+    // one launch per output parity class (1 class for stride 1)
+    for (int hp = 0; hp < d.stride; ++hp)
+      for (int wp = 0; wp < d.stride; ++wp) {
+        Launch L;
+        ConvParams& p = L.p;
+        defaults(p);
+        const int Hs = cdiv(d.H - hp, d.stride), Ws = cdiv(d.W - wp, d.stride);
+        pixel_box(Ws, Hs, d.N, 128, p);
+        int nt = 0;
+        for (int r = 0; r < d.R; ++r)
+          for (int s = 0; s < d.R; ++s) {
+            const int th = hp + d.pad - r, tw = wp + d.pad - s;
+            if (posmod(th, d.stride) || posmod(tw, d.stride)) continue;
+            TapEntry& te = p.taps[nt++];
+            te.map = 0; te.dh = (int8_t)floordiv(th, d.stride); te.dw = (int8_t)floordiv(tw, d.stride);
+            te.wtap = (int8_t)(r * d.R + s);
+          }
+        if (nt == 0) {
+          LDNN_ARG(d.accumulate, "dgrad parity class (%d,%d) has no taps and accumulate=0", hp, wp);
+          continue;
+        }
+        p.num_taps = nt;
+        p.kb_per_tap = d.Cout / 64; p.red_ch = d.Cout;
+        p.iters_total = nt * p.kb_per_tap;
+        p.out_base = ((long long)hp * d.W + wp) * d.Cin;
+        p.sW = (long long)d.stride * d.Cin; p.sH = (long long)d.stride * d.W * d.Cin; p.sN = (long long)d.H * d.W * d.Cin;
+        const int m_tiles = p.tiles_w * p.tiles_h * cdiv(d.N, p.bn), n_tiles = d.Cin / bn_;
+        finish(L, m_tiles * n_tiles);
+        L.grid = dim3(m_tiles, n_tiles, p.splits);
+        if (!dry) {
+          uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+          for (int v = 0; v < 4; ++v) { int rc = y_map(&L.maps.act[v], box); if (rc) return rc; }
+          int rc = w_map(&L.maps.other, 64);
+          if (rc) return rc;
+        }
+        plan.launches.push_back(L);
+      }
+  } else {
+    LDNN_ARG(d.Cout % 128 == 0 || d.Cout == 64, "wgrad needs Cout %% 128 == 0 (or 64)");
+    Launch L;
+    ConvParams& p = L.p;
+    defaults(p);
+    pixel_box(Q, P, d.N, 64, p);
+    fwd_taps(p);
+    p.iters_total = p.tiles_w * p.tiles_h * cdiv(d.N, p.bn);
+    p.sN = (long long)T * d.Cin;     // row stride of dw
+    p.red_ch = d.Cout;               // rows that exist (store mask)
+    const int m_tiles = cdiv(d.Cout, 128), n_tiles = d.Cin / bn_;
+    finish(L, m_tiles * n_tiles * T);
+    L.grid = dim3(m_tiles, n_tiles, T * p.splits);
+    if (!dry) {
+      uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+      const int nviews = d.stride == 1 ? 1 : 4;
+      for (int v = 0; v < 4; ++v) {
+        int rc = x_view_map(&L.maps.act[v], v < nviews ? v / 2 : 0, v < nviews ? v % 2 : 0, box);
+        if (rc) return rc;
+      }
+      int rc = y_map(&L.maps.other, box);
+      if (rc) return rc;
+    }
+    plan.launches.push_back(L);
+  }
+  plan.launches.empty() ? (void)0 : (void)0;
+  // stash totals in the first launch for the query
+  if (!plan.launches.empty()) { plan.launches[0].scratch_floats = scratch_off; plan.launches[0].tickets = ticket_off; }
+  return LDNN_OK;
+}
+
+template <int MODE, int BN>
+static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
+  using Cfg = ConvCfg<BN>;
+  static bool configured = false;
+  if (!configured) {
+    LDNN_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<MODE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   Cfg::kSmemBytes));
+    configured = true;
+  }
+  conv_gemm_kernel<MODE, BN><<<L.grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(
+      L.maps, L.p, pl.out, pl.addend, pl.scratch ? pl.scratch + L.scratch_off : nullptr,
+      pl.tickets ? pl.tickets + L.ticket_off : nullptr);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+template <int MODE>
+static int launch_bn(const Launch& L, const Plan& pl, cudaStream_t st) {
+  switch (pl.block_n) {
+    case 64: return launch_one<MODE, 64>(L, pl, st);
+    case 128: return launch_one<MODE, 128>(L, pl, st);
+    default: return launch_one<MODE, 256>(L, pl, st);
+  }
+}
+
+}  // namespace ldnn
+
+using namespace ldnn;
+
+extern "C" const char* ldnn_last_error(void) { return g_err; }
+extern "C" int ldnn_version(void) { return 100; }
+extern "C" unsigned long long ldnn_launch_count(void) { return g_launches.load(); }
+
+extern "C" int ldnn_conv_query(const ldnn_conv_desc* d, size_t* scratch_bytes, size_t* ticket_count, int* launches) {
+  Plan pl;
+  int rc = build(*d, pl, true);
+  if (rc) return rc;
+  if (scratch_bytes) *scratch_bytes = pl.launches.empty() ? 0 : pl.launches[0].scratch_floats * sizeof(float);
+  if (ticket_count) *ticket_count = pl.launches.empty() ? 0 : pl.launches[0].tickets;
+  if (launches) *launches = (int)pl.launches.size();
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_conv_plan_create(const ldnn_conv_desc* d, void** plan) {
+  Plan* pl = new Plan();
+  int rc = build(*d, *pl, false);
+  if (rc) { delete pl; return rc; }
+  bool need_scratch = false;
+  for (auto& L : pl->launches) need_scratch |= L.p.splits > 1;
+  if (need_scratch && (!d->scratch || !d->tickets)) {
+    delete pl;
+    set_last_error("conv plan uses split-K but scratch/tickets were not provided");
+    return LDNN_ERR_ARG;
+  }
+  *plan = pl;
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_conv_plan_run(void* plan, void* stream) {
+  Plan* pl = reinterpret_cast<Plan*>(plan);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  for (const Launch& L : pl->launches) {
+    int rc;
+    if (pl->mode == MODE_FPROP) rc = launch_bn<MODE_FPROP>(L, *pl, st);
+    else if (pl->mode == MODE_DGRAD) rc = launch_bn<MODE_DGRAD>(L, *pl, st);
+    else rc = launch_bn<MODE_WGRAD>(L, *pl, st);
+    if (rc) return rc;
+  }
+  return LDNN_OK;
+}
+
+extern "C" void ldnn_conv_plan_destroy(void* plan) { delete reinterpret_cast<Plan*>(plan); }

@@ -1,0 +1,299 @@
+// Implicit-GEMM convolution on tcgen05 / TMEM / TMA  (K-CONV-F / -D / -W).
+//
+// Replaces the reference's cuDNN convolutions (Balanced All-Reduce/model.py:55,57,63,78 and
+// their autograd backward, trainer.py:208).  One warp-specialised kernel, three modes:
+//
+//   FPROP  y[pix, co]   = sum_{tap, ci} x[pix (+) tap, ci] * w[co, tap, ci]
+//   DGRAD  dx[pix, ci]  = sum_{tap, co} dy[pix (-) tap, co] * w[co, tap, ci]      (B read MN-major: no transposed copy)
+//   WGRAD  dw[co,tap,ci]= sum_{pix}     dy[pix, co] * x[pix (+) tap, ci]           (A and B read MN-major)
+//
+// Activations are NHWC bf16, weights KRSC bf16 ("[Cout][R][S][Cin]").  There is no im2col
+// buffer: for every filter tap the A tile is a *shifted 4-D TMA box* of the activation tensor
+// (channels x w x h x n = 64 x bw x bh x bn, bw*bh*bn pixels), and the TMA unit's out-of-bounds
+// zero fill provides the padding.  Stride-2 convolutions use four parity views of the input
+// (one tensor map per (h%2, w%2)), which turns them into the same shifted-box loads.
+// Accumulators live in TMEM (128 lanes x BLOCK_N fp32 columns); a single elected thread issues
+// tcgen05.mma; the epilogue warps read TMEM with tcgen05.ld and write bf16 NHWC / fp32 KRSC.
+// Small-M / huge-K layers (layer3/4 at batch 64) use split-K: partial tiles go to an fp32
+// scratch slab and the last CTA to arrive on a tile (atomic ticket) reduces them in a fixed
+// order, so results are deterministic and no memset / atomics on the output are needed.
+#pragma once
+#include "ptx.cuh"
+
+namespace ldnn {
+
+enum ConvMode : int { MODE_FPROP = 0, MODE_DGRAD = 1, MODE_WGRAD = 2 };
+
+struct TapEntry {
+  int8_t map;   // which shifted-operand tensor map (parity view) this tap reads
+  int8_t dh;    // box shift in h (in units of the view's rows)
+  int8_t dw;    // box shift in w
+  int8_t wtap;  // tap index inside the weight tensor (r*S+s)
+};
+
+struct ConvParams {
+  int bw, bh, bn;          // pixel box (w, h, n); bw*bh*bn = 128 (fprop/dgrad M tile) or 64 (wgrad K block)
+  int tiles_w, tiles_h;    // boxes along w and h of the pixel grid
+  int num_taps;
+  int kb_per_tap;          // fprop/dgrad: reduction channels / 64
+  int iters_total;         // fprop/dgrad: num_taps*kb_per_tap; wgrad: number of pixel blocks
+  int iters_per_split;
+  int splits;
+  int Wd, Hd, Nd;          // extents of the pixel grid (for store masks)
+  int red_ch;              // fprop: Cin, dgrad: Cout (channels of the reduction dim) — weight column stride per tap
+  int n_total;             // total N of the GEMM (fprop: Cout, dgrad: Cin, wgrad: Cin)
+  long long out_base;      // element offset of pixel (0,0,0)
+  long long sN, sH, sW;    // output strides in elements (fprop/dgrad); wgrad: sN = row stride (T*Cin)
+  int accumulate;          // epilogue adds `addend` (same addressing as out)
+  uint32_t a_lbo, a_sbo, b_lbo, b_sbo;   // smem descriptor strides (bytes)
+  TapEntry taps[16];
+};
+
+struct ConvMaps {
+  CUtensorMap act[4];   // shifted operand (x for fprop/wgrad, dy for dgrad), one per parity view
+  CUtensorMap other;    // weights (fprop/dgrad, 2-D) or dy (wgrad, 4-D)
+};
+
+template <int BLOCK_N>
+struct ConvCfg {
+  static constexpr int kStages = (BLOCK_N == 256) ? 4 : (BLOCK_N == 128 ? 6 : 8);
+  static constexpr int kABytes = 128 * 64 * 2;
+  static constexpr int kBBytes = BLOCK_N * 64 * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int kThreads = 192;
+};
+
+template <int MODE, int BLOCK_N>
+__global__ void __launch_bounds__(192, 1)
+conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void* __restrict__ out,
+                 const void* __restrict__ addend, float* __restrict__ scratch, unsigned int* __restrict__ tickets) {
+  using Cfg = ConvCfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint32_t* last_flag = tmem_ptr + 1;
+
+  const int warp = threadIdx.x >> 5;
+  const int m_tile = blockIdx.x, n_tile = blockIdx.y;
+  int split = blockIdx.z, tap_fixed = 0;
+  if (MODE == MODE_WGRAD) { tap_fixed = blockIdx.z / p.splits; split = blockIdx.z % p.splits; }
+  const int it_begin = split * p.iters_per_split;
+  const int it_end = min(it_begin + p.iters_per_split, p.iters_total);
+  const int n0 = n_tile * BLOCK_N;
+
+  if (warp == 0 && elect_one()) {
+    for (int i = 0; i < 4; ++i) prefetch_tmap(&maps.act[i]);
+    prefetch_tmap(&maps.other);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+      mbar_init(tmem_full, 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc<BLOCK_N>(tmem_ptr);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  // pixel-tile coordinates (fprop/dgrad: the M tile; wgrad: decoded per K block)
+  auto decode = [&](int t, int& w0, int& h0, int& nn0) {
+    int wt = t % p.tiles_w;
+    int ht = (t / p.tiles_w) % p.tiles_h;
+    int nt = t / (p.tiles_w * p.tiles_h);
+    w0 = wt * p.bw; h0 = ht * p.bh; nn0 = nt * p.bn;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      int stage = 0; uint32_t phase = 0;
+      int w0 = 0, h0 = 0, nn0 = 0;
+      if (MODE != MODE_WGRAD) decode(m_tile, w0, h0, nn0);
+      for (int it = it_begin; it < it_end; ++it) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sA = smem + stage * Cfg::kStageBytes;
+        uint8_t* sB = sA + Cfg::kABytes;
+        mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+        if (MODE == MODE_FPROP || MODE == MODE_DGRAD) {
+          const int tap = it / p.kb_per_tap, kb = it - tap * p.kb_per_tap;
+          const TapEntry te = p.taps[tap];
+          tma_load_4d(sA, &maps.act[te.map], &full_bar[stage], kb * 64, w0 + te.dw, h0 + te.dh, nn0);
+          if (MODE == MODE_FPROP) {
+            // weights [Cout rows][taps*Cin cols], K-major: one box of 64 cols x BLOCK_N rows
+            tma_load_2d(sB, &maps.other, &full_bar[stage], te.wtap * p.red_ch + kb * 64, n0);
+          } else {
+            // weights [Cout rows][taps*Cin cols]; B[n=ci, k=co] is MN-major: boxes of 64 ci x 64 co
+#pragma unroll
+            for (int j = 0; j < BLOCK_N / 64; ++j)
+              tma_load_2d(sB + j * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64, kb * 64);
+          }
+        } else {
+          decode(it, w0, h0, nn0);
+          const TapEntry te = p.taps[tap_fixed];
+          // A = dy[pix][co]  (MN-major, two 64-channel boxes) ; B = x[pix (+) tap][ci] (MN-major)
+          tma_load_4d(sA, &maps.other, &full_bar[stage], m_tile * 128, w0, h0, nn0);
+          tma_load_4d(sA + 8192, &maps.other, &full_bar[stage], m_tile * 128 + 64, w0, h0, nn0);
+#pragma unroll
+          for (int j = 0; j < BLOCK_N / 64; ++j)
+            tma_load_4d(sB + j * 8192, &maps.act[te.map], &full_bar[stage], n0 + j * 64, w0 + te.dw, h0 + te.dh, nn0);
+        }
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc_bf16(128, BLOCK_N, MODE == MODE_WGRAD ? 1u : 0u,
+                                               MODE == MODE_FPROP ? 0u : 1u);
+    constexpr uint32_t a_kstep = (MODE == MODE_WGRAD) ? 2048u : 32u;
+    constexpr uint32_t b_kstep = (MODE == MODE_FPROP) ? 32u : 2048u;
+    int stage = 0; uint32_t phase = 0;
+    for (int it = it_begin; it < it_end; ++it) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t sA = smem_u32(smem + stage * Cfg::kStageBytes);
+        const uint32_t sB = sA + Cfg::kABytes;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t da = make_smem_desc_sw128(sA + k * a_kstep, p.a_lbo, p.a_sbo);
+          const uint64_t db = make_smem_desc_sw128(sB + k * b_kstep, p.b_lbo, p.b_sbo);
+          umma_bf16(tmem_base, da, db, idesc, (it > it_begin || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[stage]);                 // frees the smem slot when these MMAs retire
+        if (it == it_end - 1) umma_commit(tmem_full);   // accumulator complete
+      }
+      __syncwarp();
+      if (++stage == kStages) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int q = warp & 3;                    // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane_id();        // accumulator row == M index inside the tile
+    const int et = (warp - 2) * 32 + lane_id();  // 0..127 epilogue thread id
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+
+    // ---- where does this row go? ----
+    bool row_ok = true;
+    long long row_off;
+    if (MODE == MODE_WGRAD) {
+      row_ok = (m_tile * 128 + row) < p.red_ch;   // Cout may be 64 (< one M tile)
+      row_off = p.out_base + (long long)(m_tile * 128 + row) * p.sN + (long long)p.taps[tap_fixed].wtap * p.n_total;
+    } else {
+      int w0, h0, nn0;
+      decode(m_tile, w0, h0, nn0);
+      const int wl = row % p.bw, hl = (row / p.bw) % p.bh, nl = row / (p.bw * p.bh);
+      const int w = w0 + wl, h = h0 + hl, n = nn0 + nl;
+      row_ok = (w < p.Wd) && (h < p.Hd) && (n < p.Nd);
+      row_off = p.out_base + n * p.sN + h * p.sH + w * p.sW;
+    }
+
+    auto emit = [&](int col0, const float (&v)[32]) {
+      if (!row_ok) return;
+      if (MODE == MODE_WGRAD) {
+        float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + row_off + n0 + col0);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      } else {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + row_off + n0 + col0;
+        const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(addend) + row_off + n0 + col0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float f[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = v[8 * i + j];
+          if (p.accumulate) {
+            uint4 av = *reinterpret_cast<const uint4*>(a + 8 * i);
+            const __nv_bfloat162* ab = reinterpret_cast<const __nv_bfloat162*>(&av);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float2 t = __bfloat1622float2(ab[j]);
+              f[2 * j] += t.x; f[2 * j + 1] += t.y;
+            }
+          }
+          uint4 ov;
+          __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(&ov);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) ob[j] = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+          *reinterpret_cast<uint4*>(o + 8 * i) = ov;
+        }
+      }
+    };
+
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    if (p.splits == 1) {
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c, r);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+        emit(c, v);
+      }
+    } else {
+      // ---- split-K: park the partial tile, take a ticket, last arriver reduces ----
+      const int tiles_n = gridDim.y;
+      const long long tile_lin = (MODE == MODE_WGRAD)
+                                     ? ((long long)tap_fixed * gridDim.x + m_tile) * tiles_n + n_tile
+                                     : (long long)m_tile * tiles_n + n_tile;
+      float4* part = reinterpret_cast<float4*>(scratch) + (tile_lin * p.splits + split) * (BLOCK_N / 4) * 128;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          part[(c / 4 + i) * 128 + row] = make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]),
+                                                      __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
+      }
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (et == 0) {
+        const unsigned int old = atomicAdd(&tickets[tile_lin], 1u);
+        *last_flag = (old == static_cast<unsigned int>(p.splits - 1)) ? 1u : 0u;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (*last_flag) {
+        __threadfence();
+        const float4* base = reinterpret_cast<const float4*>(scratch) + tile_lin * p.splits * (BLOCK_N / 4) * 128;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N; c += 32) {
+          float v[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = 0.f;
+          for (int s = 0; s < p.splits; ++s) {
+            const float4* ps = base + (long long)s * (BLOCK_N / 4) * 128;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float4 t = __ldcg(&ps[(c / 4 + i) * 128 + row]);
+              v[4 * i] += t.x; v[4 * i + 1] += t.y; v[4 * i + 2] += t.z; v[4 * i + 3] += t.w;
+            }
+          }
+          emit(c, v);
+        }
+        if (et == 0) tickets[tile_lin] = 0;   // ready for the next launch
+      }
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<BLOCK_N>(tmem_base);
+  }
+}
+
+}  // namespace ldnn

@@ -1,0 +1,188 @@
+// K-HEAD: global-average-pool + linear + softmax cross-entropy forward AND backward, with the
+// correct-prediction count and the fc gradients, in two launches and no host sync
+// (replaces Balanced All-Reduce/model.py:99-100,108-110; main.py:52; trainer.py:207,212-216 —
+// upstream reads loss/accuracy back with three .item() calls per batch).
+// K-OPT: Adam / SGD-momentum on flat fp32 slabs + bf16 compute copy (trainer.py:205,210,218).
+#include "../include/ldnn_b200.h"
+#include "common.cuh"
+#include "optim.cuh"
+#include <atomic>
+
+namespace ldnn {
+extern std::atomic<unsigned long long> g_launches;
+
+constexpr int kMaxClasses = 1024;
+
+// one CTA per sample
+__global__ void __launch_bounds__(256)
+head_sample_kernel(const __nv_bfloat16* __restrict__ act, int HW, int C, int classes, const float* __restrict__ fc_w,
+                   const float* __restrict__ fc_b, const long long* __restrict__ labels, float* __restrict__ pooled,
+                   float* __restrict__ logits, float* __restrict__ dlogits, float* __restrict__ loss_n,
+                   float* __restrict__ correct_n, long long* __restrict__ pred, __nv_bfloat16* __restrict__ dact,
+                   int training, float inv_batch) {
+  extern __shared__ float sm[];          // pooled[C] | logits[classes] | dl[classes]
+  float* sp = sm;
+  float* sl = sm + C;
+  float* sd = sl + classes;
+  const int n = blockIdx.x;
+  const __nv_bfloat16* a = act + (size_t)n * HW * C;
+  const float inv_hw = 1.f / (float)HW;
+  for (int c = threadIdx.x * 2; c < C; c += blockDim.x * 2) {
+    float s0 = 0.f, s1 = 0.f;
+    for (int p = 0; p < HW; ++p) {
+      const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(a + (size_t)p * C + c));
+      s0 += t.x; s1 += t.y;
+    }
+    sp[c] = s0 * inv_hw; sp[c + 1] = s1 * inv_hw;
+    pooled[(size_t)n * C + c] = sp[c];
+    pooled[(size_t)n * C + c + 1] = sp[c + 1];
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (int j = warp; j < classes; j += nwarps) {
+    float s = 0.f;
+    for (int c = lane; c < C; c += 32) s += sp[c] * fc_w[(size_t)j * C + c];
+    s = warp_sum(s);
+    if (lane == 0) { sl[j] = s + fc_b[j]; logits[(size_t)n * classes + j] = sl[j]; }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    float mx = -INFINITY; int arg = 0;
+    for (int j = lane; j < classes; j += 32) if (sl[j] > mx) { mx = sl[j]; arg = j; }
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+      if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
+    }
+    float se = 0.f;
+    for (int j = lane; j < classes; j += 32) se += __expf(sl[j] - mx);
+    se = warp_sum(se);
+    const int lab = (int)labels[n];
+    const float lse = mx + __logf(se);
+    if (lane == 0) {
+      loss_n[n] = lse - sl[lab];
+      correct_n[n] = (arg == lab) ? 1.f : 0.f;
+      pred[n] = arg;
+    }
+    for (int j = lane; j < classes; j += 32) {
+      const float pj = __expf(sl[j] - lse);
+      const float d = (pj - (j == lab ? 1.f : 0.f)) * inv_batch;
+      sd[j] = d;
+      dlogits[(size_t)n * classes + j] = d;
+    }
+  }
+  if (!training) return;
+  __syncthreads();
+  // d_act[n, p, c] = (1/HW) * sum_j dl[j] * W[j, c]   (same for every pixel p)
+  for (int c = threadIdx.x * 2; c < C; c += blockDim.x * 2) {
+    float g0 = 0.f, g1 = 0.f;
+    for (int j = 0; j < classes; ++j) {
+      const float2 w = *reinterpret_cast<const float2*>(fc_w + (size_t)j * C + c);
+      g0 += sd[j] * w.x; g1 += sd[j] * w.y;
+    }
+    const __nv_bfloat162 v = __floats2bfloat162_rn(g0 * inv_hw, g1 * inv_hw);
+    for (int p = 0; p < HW; ++p)
+      *reinterpret_cast<__nv_bfloat162*>(dact + ((size_t)n * HW + p) * C + c) = v;
+  }
+}
+
+// fc gradients (deterministic sums over the batch) + batch loss / correct totals
+__global__ void __launch_bounds__(256)
+head_reduce_kernel(const float* __restrict__ pooled, const float* __restrict__ dlogits,
+                   const float* __restrict__ loss_n, const float* __restrict__ correct_n, int N, int C, int classes,
+                   float* __restrict__ dfc_w, float* __restrict__ dfc_b, float* __restrict__ loss_out,
+                   float* __restrict__ correct_out, int training) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (training && c < C) {
+    for (int j = 0; j < classes; ++j) {
+      float s = 0.f;
+      for (int n = 0; n < N; ++n) s += dlogits[(size_t)n * classes + j] * pooled[(size_t)n * C + c];
+      dfc_w[(size_t)j * C + c] = s;
+    }
+  }
+  if (blockIdx.x == 0) {
+    if (training)
+      for (int j = threadIdx.x; j < classes; j += blockDim.x) {
+        float s = 0.f;
+        for (int n = 0; n < N; ++n) s += dlogits[(size_t)n * classes + j];
+        dfc_b[j] = s;
+      }
+    if (threadIdx.x < 32) {
+      float l = 0.f, k = 0.f;
+      for (int n = threadIdx.x; n < N; n += 32) { l += loss_n[n]; k += correct_n[n]; }
+      l = warp_sum(l); k = warp_sum(k);
+      if (threadIdx.x == 0) { *loss_out = l / (float)N; *correct_out = k; }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ optimizer
+__global__ void __launch_bounds__(256)
+optim_kernel(float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ m, float* __restrict__ v,
+             __nv_bfloat16* __restrict__ shadow, long long n4, const ldnn_optim o) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
+       i += (long long)gridDim.x * blockDim.x) {
+    float4 p = reinterpret_cast<float4*>(params)[i];
+    float4 g = reinterpret_cast<const float4*>(grads)[i];
+    float4 mm = reinterpret_cast<float4*>(m)[i];
+    float4 vv = o.kind == 0 ? reinterpret_cast<float4*>(v)[i] : make_float4(0, 0, 0, 0);
+    optim_update4(p, g, mm, vv, o);
+    reinterpret_cast<float4*>(params)[i] = p;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    if (o.kind == 0) reinterpret_cast<float4*>(v)[i] = vv;
+    if (shadow) store_bf16x4(shadow + 4 * i, p);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n4) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
+       i += (long long)gridDim.x * blockDim.x)
+    store_bf16x4(dst + 4 * i, reinterpret_cast<const float4*>(src)[i]);
+}
+
+}  // namespace ldnn
+
+using namespace ldnn;
+
+extern "C" int ldnn_head_fwd_bwd(const void* act, int N, int HW, int C, int classes, const float* fc_w,
+                                 const float* fc_b, const long long* labels, float* pooled, float* logits,
+                                 float* dlogits, float* loss_n, float* correct_n, long long* pred, void* dact,
+                                 float* dfc_w, float* dfc_b, float* loss_out, float* correct_out, int training,
+                                 void* stream) {
+  LDNN_ARG(C % 2 == 0 && classes <= kMaxClasses, "head: C=%d classes=%d", C, classes);
+  const size_t smem = (size_t)(C + 2 * classes) * sizeof(float);
+  head_sample_kernel<<<N, 256, smem, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)act, HW, C, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,
+      (__nv_bfloat16*)dact, training, 1.f / (float)N);
+  g_launches.fetch_add(1);
+  LDNN_CUDA(cudaGetLastError());
+  head_reduce_kernel<<<(C + 255) / 256, 256, 0, (cudaStream_t)stream>>>(pooled, dlogits, loss_n, correct_n, N, C,
+                                                                       classes, dfc_w, dfc_b, loss_out, correct_out,
+                                                                       training);
+  g_launches.fetch_add(1);
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_optim_step(float* params, const float* grads, float* m, float* v, void* shadow_bf16, long long n,
+                               const ldnn_optim* o, void* stream) {
+  LDNN_ARG(n % 4 == 0, "optim: n=%lld must be a multiple of 4", n);
+  LDNN_ARG(o->kind == 1 || v != nullptr, "adam needs v");
+  const long long n4 = n / 4;
+  const int blocks = (int)std::min<long long>((n4 + 255) / 256, 148 * 8);
+  optim_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(params, grads, m, v, (__nv_bfloat16*)shadow_bf16, n4, *o);
+  g_launches.fetch_add(1);
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_cast_bf16(const float* src, void* dst, long long n, void* stream) {
+  LDNN_ARG(n % 4 == 0, "cast: n %% 4");
+  const long long n4 = n / 4;
+  const int blocks = (int)std::min<long long>((n4 + 255) / 256, 148 * 8);
+  cast_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, n4);
+  g_launches.fetch_add(1);
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}

@@ -173,7 +173,8 @@ class TorchEngine(Engine):
             xavier_init_(self.model)
         self.model.to(self.device)
         slots, total = build_layout([(k, tuple(p.shape)) for k, p in self.model.named_parameters()])
-        self.flat = FlatState(slots, total, self.device, opt)
+        self._symm = {}
+        self.flat = FlatState(slots, total, self.device, opt, allocator=self._symm_allocator())
         # re-seat every parameter (and its grad) as a view of the flat slabs
         with torch.no_grad():
             for k, p in self.model.named_parameters():
@@ -181,6 +182,27 @@ class TorchEngine(Engine):
                 v.copy_(p.data)
                 p.data = v
                 p.grad = self.flat.view(self.flat.grads, k)
+
+    def _symm_allocator(self):
+        """On CUDA the flat slabs live in IPC-shareable memory so the fused P2P exchange can
+        map them into the peers; on CPU they are ordinary tensors."""
+        if self.device.type != "cuda":
+            return None
+        from .ops import _lib as L
+        if not L.available():
+            return None
+        from .ops import native_ops as K
+
+        def alloc(n):
+            t, handle, ptr = K.symm_alloc(n * 4, self.device)
+            self._symm[["params", "grads", "m", "v"][len(self._symm)]] = (t, handle, ptr)
+            return t.view(torch.float32)
+        return alloc
+
+    def symm_handle(self, name: str):
+        if name not in self._symm:
+            raise RuntimeError("flat slabs are not in symmetric memory (CPU engine or library not built)")
+        return self._symm[name][1], self._symm[name][2], self.flat.total * 4
 
     def train_step(self, x, y, update: bool = True):
         self.model.train()

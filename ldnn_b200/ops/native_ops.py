@@ -1,0 +1,181 @@
+"""Python faces of the sm_100a kernels (thin: pointer plumbing only).
+
+Every function launches on the *current* torch CUDA stream, so the calls compose with
+``torch.cuda.graph`` capture and with side streams.  Layout conventions:
+activations NHWC bf16, conv weights KRSC bf16 (``[Cout][R*S*Cin]``), statistics fp32.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+
+FPROP, DGRAD, WGRAD = 0, 1, 2
+
+
+class ConvPlan:
+    """A bound, reusable convolution launch (tensor maps + tiling + split-K workspace).
+    Pointers are baked in — the static-graph executor owns fixed buffers."""
+
+    def __init__(self, mode: int, N: int, H: int, W: int, Cin: int, Cout: int, R: int, stride: int, pad: int,
+                 x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, dw: Optional[torch.Tensor] = None,
+                 addend: Optional[torch.Tensor] = None, accumulate: bool = False, block_n: int = 0, splits: int = 0,
+                 workspace=None, desc_override=None):
+        d = L.ConvDesc()
+        d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
+        d.block_n, d.splits, d.accumulate = block_n, splits, int(accumulate)
+        d.x, d.w, d.y = x.data_ptr(), (0 if w is None else w.data_ptr()), y.data_ptr()
+        d.dw = 0 if dw is None else dw.data_ptr()
+        d.addend = 0 if addend is None else addend.data_ptr()
+        if desc_override:
+            d.a_lbo, d.a_sbo, d.b_lbo, d.b_sbo = desc_override
+        sb, tk, nl = C.c_size_t(0), C.c_size_t(0), C.c_int(0)
+        L.check(L.lib().ldnn_conv_query(C.byref(d), C.byref(sb), C.byref(tk), C.byref(nl)))
+        self.scratch_bytes, self.ticket_count, self.num_launches = sb.value, tk.value, nl.value
+        self._keep = [x, w, y, dw, addend]
+        if sb.value:
+            if workspace is not None:
+                scratch, tickets = workspace.take(sb.value, tk.value)
+            else:
+                scratch = torch.empty(sb.value // 4, dtype=torch.float32, device=x.device)
+                tickets = torch.zeros(tk.value, dtype=torch.int32, device=x.device)
+            d.scratch, d.tickets = scratch.data_ptr(), tickets.data_ptr()
+            self._keep += [scratch, tickets]
+        self._plan = C.c_void_p(0)
+        L.check(L.lib().ldnn_conv_plan_create(C.byref(d), C.byref(self._plan)))
+
+    def run(self) -> None:
+        L.check(L.lib().ldnn_conv_plan_run(self._plan, L.stream_ptr()))
+
+    def __del__(self):
+        try:
+            if self._plan:
+                L.lib().ldnn_conv_plan_destroy(self._plan)
+        except Exception:
+            pass
+
+
+class Workspace:
+    """Split-K scratch shared by every plan of an executor.  Plans run one after another
+    on one stream, so they can share the partial-tile slab; tickets are per plan
+    (they must stay zero between launches of the same plan)."""
+
+    def __init__(self, device):
+        self.device = device
+        self.scratch: Optional[torch.Tensor] = None
+        self.need = 0
+        self.tickets = []
+
+    def take(self, scratch_bytes: int, ticket_count: int):
+        self.need = max(self.need, scratch_bytes)
+        if self.scratch is None or self.scratch.numel() * 4 < self.need:
+            raise RuntimeError("Workspace.reserve() must run before plans are created")
+        t = torch.zeros(max(ticket_count, 1), dtype=torch.int32, device=self.device)
+        self.tickets.append(t)
+        return self.scratch, t
+
+    def reserve(self, nbytes: int):
+        self.need = max(self.need, nbytes)
+        self.scratch = torch.empty(max(self.need // 4, 1), dtype=torch.float32, device=self.device)
+
+
+def conv_query(mode, N, H, W, Cin, Cout, R, stride, pad, block_n=0, splits=0, accumulate=True):
+    d = L.ConvDesc()
+    d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
+    d.block_n, d.splits, d.accumulate = block_n, splits, int(accumulate)
+    sb, tk, nl = C.c_size_t(0), C.c_size_t(0), C.c_int(0)
+    L.check(L.lib().ldnn_conv_query(C.byref(d), C.byref(sb), C.byref(tk), C.byref(nl)))
+    return sb.value, tk.value, nl.value
+
+
+def im2col_stem(x_nchw_f32, col_bf16, N, Cc, H, W, R, stride, pad, Kpad):
+    L.check(L.lib().ldnn_im2col_stem(L.ptr(x_nchw_f32), L.ptr(col_bf16), N, Cc, H, W, R, stride, pad, Kpad,
+                                     L.stream_ptr()))
+
+
+def bn_fwd_stats(y, M, Cc, chunks, partial, ticket, gamma, beta, rmean, rvar, nbt, save_mean, save_invstd, scale,
+                 shift, eps=1e-5, momentum=0.1):
+    L.check(L.lib().ldnn_bn_fwd_stats(L.ptr(y), M, Cc, chunks, L.ptr(partial), L.ptr(ticket), L.ptr(gamma),
+                                      L.ptr(beta), L.ptr(rmean), L.ptr(rvar), L.ptr(nbt), L.ptr(save_mean),
+                                      L.ptr(save_invstd), L.ptr(scale), L.ptr(shift), C.c_float(eps),
+                                      C.c_float(momentum), L.stream_ptr()))
+
+
+def bn_eval_coeffs(gamma, beta, rmean, rvar, scale, shift, Cc, eps=1e-5):
+    L.check(L.lib().ldnn_bn_eval_coeffs(L.ptr(gamma), L.ptr(beta), L.ptr(rmean), L.ptr(rvar), L.ptr(scale),
+                                        L.ptr(shift), Cc, C.c_float(eps), L.stream_ptr()))
+
+
+def bn_fwd_apply(y, scale, shift, residual, out, M, Cc, relu):
+    L.check(L.lib().ldnn_bn_fwd_apply(L.ptr(y), L.ptr(scale), L.ptr(shift), L.ptr(residual), L.ptr(out), M, Cc,
+                                      int(relu), L.stream_ptr()))
+
+
+def bn_bwd_reduce(dout, out, y, save_mean, save_invstd, partial, ticket, M, Cc, chunks, relu, dgamma, dbeta):
+    L.check(L.lib().ldnn_bn_bwd_reduce(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
+                                       L.ptr(partial), L.ptr(ticket), M, Cc, chunks, int(relu), L.ptr(dgamma),
+                                       L.ptr(dbeta), L.stream_ptr()))
+
+
+def bn_bwd_apply(dout, out, y, save_mean, save_invstd, gamma, dgamma, dbeta, dy_raw, dres, M, Cc, relu,
+                 res_accumulate):
+    L.check(L.lib().ldnn_bn_bwd_apply(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
+                                      L.ptr(gamma), L.ptr(dgamma), L.ptr(dbeta), L.ptr(dy_raw), L.ptr(dres), M, Cc,
+                                      int(relu), int(res_accumulate), L.stream_ptr()))
+
+
+def maxpool_fwd(x, y, N, H, W, Cc, k, stride, pad):
+    L.check(L.lib().ldnn_maxpool_fwd(L.ptr(x), L.ptr(y), N, H, W, Cc, k, stride, pad, L.stream_ptr()))
+
+
+def maxpool_bwd(x, y, dy, dx, N, H, W, Cc, k, stride, pad):
+    L.check(L.lib().ldnn_maxpool_bwd(L.ptr(x), L.ptr(y), L.ptr(dy), L.ptr(dx), N, H, W, Cc, k, stride, pad,
+                                     L.stream_ptr()))
+
+
+def head_fwd_bwd(act, N, HW, Cc, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,
+                 dact, dfc_w, dfc_b, loss_out, correct_out, training):
+    L.check(L.lib().ldnn_head_fwd_bwd(L.ptr(act), N, HW, Cc, classes, L.ptr(fc_w), L.ptr(fc_b), L.ptr(labels),
+                                      L.ptr(pooled), L.ptr(logits), L.ptr(dlogits), L.ptr(loss_n), L.ptr(correct_n),
+                                      L.ptr(pred), L.ptr(dact), L.ptr(dfc_w), L.ptr(dfc_b), L.ptr(loss_out),
+                                      L.ptr(correct_out), int(training), L.stream_ptr()))
+
+
+def optim_step(params, grads, m, v, shadow, n, opt_struct):
+    L.check(L.lib().ldnn_optim_step(L.ptr(params), L.ptr(grads), L.ptr(m), L.ptr(v), L.ptr(shadow),
+                                    C.c_longlong(n), C.byref(opt_struct), L.stream_ptr()))
+
+
+def cast_bf16(src, dst, n):
+    L.check(L.lib().ldnn_cast_bf16(L.ptr(src), L.ptr(dst), C.c_longlong(n), L.stream_ptr()))
+
+
+# ---- torch-tensor wrapper around raw (cudaMalloc'd / IPC-mapped) device memory -------------
+class _RawCuda:
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+def tensor_from_ptr(ptr: int, nbytes: int, dtype: torch.dtype, device) -> torch.Tensor:
+    t = torch.as_tensor(_RawCuda(ptr, nbytes), device=device)
+    return t.view(dtype)
+
+
+def symm_alloc(nbytes: int, device):
+    """cudaMalloc through the library (IPC-shareable).  Returns (tensor<uint8>, handle bytes, raw ptr)."""
+    p = C.c_void_p(0)
+    h = (C.c_ubyte * 64)()
+    with torch.cuda.device(device):
+        L.check(L.lib().ldnn_symm_alloc(C.c_size_t(nbytes), C.byref(p), h))
+    return tensor_from_ptr(p.value, nbytes, torch.uint8, device), bytes(h), p.value
+
+
+def symm_open(handle: bytes, nbytes: int, device):
+    p = C.c_void_p(0)
+    buf = (C.c_ubyte * 64).from_buffer_copy(handle)
+    with torch.cuda.device(device):
+        L.check(L.lib().ldnn_symm_open(buf, C.byref(p)))
+    return p.value

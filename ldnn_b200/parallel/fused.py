@@ -1,0 +1,214 @@
+"""FusedExchanger — the product path of the exchange layer.
+
+Every topology's exchange is one hand-written sm_100a kernel (``csrc/comm.cu``) that reads
+and writes the peers' flat slabs directly over NVLink/NVSwitch and runs the per-rank weight,
+the optimizer update and the bf16 cast in the same pass:
+
+=============  ===================  =========================================================
+topology       semantics            kernel
+=============  ===================  =========================================================
+allreduce      (always global)      ``ldnn_allreduce_fused`` two-shot: pull-reduce the owned
+                                    slice, fused tail, push to every peer
+ring           allreduce            ``ldnn_ring_fused(num_rings=1)`` RS+AG around one ring
+double_ring    allreduce            ``ldnn_ring_fused(num_rings=2)`` two counter-rotating rings,
+                                    each on half of the slab
+ring / dring   gossip (reference)   ``ldnn_gossip_pull`` 1-/2-hop neighbour mix, out of place
+=============  ===================  =========================================================
+
+Replaces ``average_*`` (BalAR/communication.py:4-31), ``ring_all_reduce_*``
+(BalR/communication.py:5-62), ``double_ring_all_reduce*`` (BalDR/communication.py:5-77) and the
+per-parameter driver loops (BalR/trainer.py:147-168).  torch.distributed is used only to
+exchange the 64-byte CUDA-IPC handles at start-up (control plane).
+
+Self-weighted averaging (``--aggregation_type weighted``) has a rank-dependent result, which a
+reduce-scatter cannot carry around a ring; it runs on the two-shot kernel's SELFMIX form for
+every topology when ``semantics == "allreduce"``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib as L
+from ..ops import native_ops as K
+from .exchange import ExchangeSpec, gossip_coefficients, reduce_form
+
+SM_CLOCK_KHZ = 1_900_000
+
+
+class SymmetricBuffer:
+    """A local slab + the peers' mappings of the same slab (pointer table indexed by rank)."""
+
+    def __init__(self, name: str, local_ptr: int, handle: bytes, nbytes: int, rt):
+        self.name, self.nbytes = name, nbytes
+        self.ptrs: List[int] = [0] * rt.world_size
+        self.ptrs[rt.rank] = local_ptr
+        if rt.world_size > 1:
+            handles: List[Optional[bytes]] = [None] * rt.world_size
+            dist.all_gather_object(handles, handle)
+            for r, h in enumerate(handles):
+                if r != rt.rank:
+                    self.ptrs[r] = K.symm_open(h, nbytes, rt.device)
+
+    def table(self):
+        arr = (C.c_void_p * L.MAX_RANKS)()
+        for i, p in enumerate(self.ptrs):
+            arr[i] = p
+        return arr
+
+
+class FusedExchanger:
+    def __init__(self, spec: ExchangeSpec, rt, engine, comm_blocks: int = 0, watchdog_ms: int = 20000):
+        self.spec, self.rt, self.engine = spec, rt, engine
+        self.rank, self.world = rt.rank, rt.world_size
+        if self.world > L.MAX_RANKS:
+            raise L.LdnnError(f"fused exchange supports up to {L.MAX_RANKS} ranks on one NVSwitch domain")
+        if not hasattr(engine, "symm_handle"):
+            raise L.LdnnError("engine does not keep its flat slabs in symmetric memory")
+        self.blocks = comm_blocks or 64
+        self.timeout_cycles = int(watchdog_ms * SM_CLOCK_KHZ)
+        self.epoch = 0
+        self.launches = 0
+        dev = rt.device
+        self._bufs = {}
+        for name in ("params", "grads"):
+            h, p, nb = engine.symm_handle(name)
+            self._bufs[name] = SymmetricBuffer(name, p, h, nb, rt)
+        t, h, p = K.symm_alloc(L.SIGNAL_WORDS * 4, dev)
+        self._signal_t = t
+        self._bufs["signal"] = SymmetricBuffer("signal", p, h, L.SIGNAL_WORDS * 4, rt)
+        self._recv = None
+        self.error_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.n = engine.flat.total
+        if self.world > 1:
+            dist.barrier()
+
+    # ------------------------------------------------------------------ plumbing
+    def _recv_buf(self) -> SymmetricBuffer:
+        if self._recv is None:
+            t, h, p = K.symm_alloc(self.n * 4, self.rt.device)
+            self._recv_t = t
+            self._recv = SymmetricBuffer("recv", p, h, self.n * 4, self.rt)
+            if self.world > 1:
+                dist.barrier()
+        return self._recv
+
+    def _comm(self) -> L.Comm:
+        self.epoch += 1
+        c = L.Comm()
+        c.rank, c.world, c.emulate, c.blocks = self.rank, self.world, 0, self.blocks
+        c.epoch, c.timeout_cycles = self.epoch, self.timeout_cycles
+        sig = self._bufs["signal"].table()
+        for i in range(L.MAX_RANKS):
+            c.signal[i] = sig[i]
+        c.error_flag = self.error_flag.data_ptr()
+        return c
+
+    def set_shard_weights(self, w) -> None:
+        self.spec.shard_weights = list(w)
+
+    def _exchange_struct(self, data: str, mode: int, opt=None) -> L.Exchange:
+        e = L.Exchange()
+        tab = self._bufs[data].table()
+        ptab = self._bufs["params"].table()
+        for i in range(L.MAX_RANKS):
+            e.grads[i], e.params[i] = tab[i], ptab[i]
+        f = self.engine.flat
+        e.m, e.v = f.m.data_ptr(), (f.v.data_ptr() if f.v is not None else 0)
+        sh = getattr(self.engine, "shadow", None)
+        e.shadow = 0 if sh is None else sh.data_ptr()
+        e.n = self.n
+        a, b = reduce_form(self.spec, self.rank)
+        for i in range(self.world):
+            e.weight[i] = b[i]
+        e.self_coef = a
+        if a != 0.0:
+            mode |= L.X_SELFMIX
+            rtab = self._recv_buf().table()
+            for i in range(L.MAX_RANKS):
+                e.recv[i] = rtab[i]
+        e.mode = mode
+        if opt is not None:
+            e.opt = opt
+        return e
+
+    def _launch_reduce(self, e: L.Exchange) -> None:
+        c = self._comm()
+        lib, st = L.lib(), L.stream_ptr()
+        if self.spec.topology == "allreduce" or (e.mode & L.X_SELFMIX):
+            L.check(lib.ldnn_allreduce_fused(C.byref(c), C.byref(e), st))
+        else:
+            rings = 1 if self.spec.topology == "ring" else 2
+            L.check(lib.ldnn_ring_fused(C.byref(c), C.byref(e), rings, st))
+        self.launches += 1
+
+    def _gossip(self, data: str) -> None:
+        c_self, nbrs = gossip_coefficients(self.spec, self.rank)
+        c = self._comm()
+        offs = (C.c_int * 2)(*([d for d, _ in nbrs] + [0, 0])[:2])
+        coefs = (C.c_float * 2)(*([w for _, w in nbrs] + [0.0, 0.0])[:2])
+        L.check(L.lib().ldnn_gossip_pull(C.byref(c), self._bufs[data].table(), self._recv_buf().table(),
+                                         C.c_longlong(self.n), C.c_float(c_self), len(nbrs), offs, coefs,
+                                         L.stream_ptr()))
+        self.launches += 1
+
+    # ------------------------------------------------------------------ engine-level API
+    def exchange_grads(self, engine, apply_update: bool = False) -> None:
+        f = engine.flat
+        if self.spec.is_gossip():
+            self._gossip("grads")
+            if apply_update:
+                engine.local_update() if hasattr(engine, "local_update") else (f.optimizer_step(), engine.params_changed())
+            return
+        if apply_update:
+            f.step += 1
+            e = self._exchange_struct("grads", L.X_UPDATE, L.make_optim(f.opt, f.step, f.lr))
+        else:
+            e = self._exchange_struct("grads", 0)
+        self._launch_reduce(e)
+        if apply_update and getattr(engine, "shadow", None) is None:
+            engine.params_changed()
+
+    def exchange_weights(self, engine) -> None:
+        if self.spec.is_gossip():
+            self._gossip("params")
+        else:
+            self._launch_reduce(self._exchange_struct("params", L.X_CAST))
+        if getattr(engine, "shadow", None) is None or self.spec.is_gossip():
+            engine.params_changed()
+
+    def broadcast_state(self, engine, src: int = 0) -> None:
+        """C1: flat parameters by one P2P pull; BN buffers (tiny) over the control plane."""
+        if self.world == 1:
+            return
+        c = self._comm()
+        L.check(L.lib().ldnn_broadcast(C.byref(c), self._bufs["params"].table(), C.c_size_t(self.n * 4), src,
+                                       L.stream_ptr()))
+        self.launches += 1
+        for name in ("running_mean", "running_var", "nbt"):
+            t = getattr(engine, name, None)
+            if t is not None:
+                dist.broadcast(t, src=src)
+        if hasattr(engine, "model"):
+            for b in engine.model.buffers():
+                dist.broadcast(b, src=src)
+        engine.params_changed()
+        self.check()
+
+    def barrier(self) -> None:
+        c = self._comm()
+        L.check(L.lib().ldnn_barrier(C.byref(c), L.stream_ptr()))
+
+    def check(self) -> None:
+        """Raise if a device-side watchdog fired (a peer never arrived)."""
+        torch.cuda.synchronize(self.rt.device)
+        if int(self.error_flag.item()) != 0:
+            raise L.LdnnError("exchange watchdog expired: a peer did not reach the flag in time")
+
+    def close(self) -> None:
+        torch.cuda.synchronize(self.rt.device)
+        if self.world > 1:
+            dist.barrier()

@@ -1,0 +1,130 @@
+"""Fused BN(+residual,+ReLU) fwd/bwd, the pool+fc+CE head and the flat optimizer vs fp32 torch."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("M,C", [(64 * 32 * 32, 64), (64 * 16 * 16, 128), (64 * 2 * 2, 1024), (6 * 8 * 8, 256),
+                                 (37, 2048), (100, 192)])
+@pytest.mark.parametrize("relu,use_res", [(True, True), (True, False), (False, False)])
+def test_bn_forward_backward(M, C, relu, use_res):
+    from ldnn_b200.ops import native_ops as K
+    dev = "cuda"
+    g = torch.Generator().manual_seed(M + C)
+    y = (torch.randn(M, C, generator=g) * 2 + 0.5).to(dev).bfloat16()
+    res = torch.randn(M, C, generator=g).to(dev).bfloat16() if use_res else None
+    dout = torch.randn(M, C, generator=g).to(dev).bfloat16()
+    gamma = (torch.rand(C, generator=g) + 0.5).to(dev)
+    beta = torch.randn(C, generator=g).to(dev)
+    rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    nbt = torch.zeros(1, dtype=torch.int64, device=dev)
+    chunks = max(1, min(296, M // 32))
+    partial = torch.zeros(chunks * 2 * C, device=dev)
+    ticket = torch.zeros(2, dtype=torch.int32, device=dev)
+    sm, si, sc, sh = (torch.zeros(C, device=dev) for _ in range(4))
+    out = torch.empty(M, C, device=dev, dtype=torch.bfloat16)
+    for _ in range(2):        # twice: tickets must self-reset
+        K.bn_fwd_stats(y, M, C, chunks, partial, ticket, gamma, beta, rm, rv, nbt, sm, si, sc, sh)
+        K.bn_fwd_apply(y, sc, sh, res, out, M, C, relu)
+    # reference (fp32 on the same bf16 inputs)
+    yr = y.float().requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rrm, rrv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    for _ in range(2):
+        o = F.batch_norm(yr, rrm, rrv, gr, br, True, 0.1, 1e-5)
+    rr = res.float().requires_grad_(True) if use_res else None
+    if use_res:
+        o = o + rr
+    if relu:
+        o = F.relu(o)
+    assert torch.allclose(out.float(), o, atol=3e-2, rtol=2e-2)
+    assert torch.allclose(rm, rrm, atol=1e-4) and torch.allclose(rv, rrv, atol=1e-3, rtol=1e-3)
+    assert int(nbt) == 2
+    # backward; the kernel masks with its own bf16 output, mirror that in the reference
+    dgamma, dbeta = torch.zeros(C, device=dev), torch.zeros(C, device=dev)
+    dyr = torch.empty(M, C, device=dev, dtype=torch.bfloat16)
+    dres = torch.empty(M, C, device=dev, dtype=torch.bfloat16) if use_res else None
+    K.bn_bwd_reduce(dout, out, y, sm, si, partial, ticket[1:], M, C, chunks, relu, dgamma, dbeta)
+    K.bn_bwd_apply(dout, out, y, sm, si, gamma, dgamma, dbeta, dyr, dres, M, C, relu, False)
+    o.backward(dout.float())
+    scale = float(yr.grad.abs().max()) + 1e-6
+    assert float((dyr.float() - yr.grad).abs().max()) / scale < 3e-2
+    assert torch.allclose(dgamma, gr.grad, rtol=2e-2, atol=2e-2 * float(gr.grad.abs().max()))
+    assert torch.allclose(dbeta, br.grad, rtol=2e-2, atol=2e-2 * float(br.grad.abs().max()))
+    if use_res:
+        assert torch.allclose(dres.float(), rr.grad, atol=2e-2, rtol=2e-2)
+
+
+def test_bn_eval_coeffs():
+    from ldnn_b200.ops import native_ops as K
+    C = 256
+    g, b, rm = torch.rand(C, device="cuda") + 0.5, torch.randn(C, device="cuda"), torch.randn(C, device="cuda")
+    rv = torch.rand(C, device="cuda") + 0.1
+    sc, sh = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
+    K.bn_eval_coeffs(g, b, rm, rv, sc, sh, C)
+    y = torch.randn(50, C, device="cuda").bfloat16()
+    out = torch.empty_like(y)
+    K.bn_fwd_apply(y, sc, sh, None, out, 50, C, False)
+    ref = F.batch_norm(y.float(), rm, rv, g, b, False, 0.1, 1e-5)
+    assert torch.allclose(out.float(), ref, atol=3e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("N,HW,C,classes", [(64, 4, 1024, 10), (7, 4, 1024, 10), (16, 49, 2048, 1000)])
+def test_head(N, HW, C, classes):
+    from ldnn_b200.ops import native_ops as K
+    dev = "cuda"
+    g = torch.Generator().manual_seed(N)
+    act = torch.randn(N, HW, C, generator=g).to(dev).bfloat16()
+    fw = (torch.randn(classes, C, generator=g) / math.sqrt(C)).to(dev)
+    fb = torch.randn(classes, generator=g).to(dev) * 0.1
+    labels = torch.randint(0, classes, (N,), generator=g).to(dev)
+    f = lambda *s: torch.zeros(*s, device=dev)
+    pooled, logits, dlogits, loss_n, correct_n = f(N, C), f(N, classes), f(N, classes), f(N), f(N)
+    pred = torch.zeros(N, dtype=torch.int64, device=dev)
+    dact = torch.zeros(N, HW, C, device=dev, dtype=torch.bfloat16)
+    dfw, dfb, loss, correct = f(classes, C), f(classes), f(1), f(1)
+    K.head_fwd_bwd(act, N, HW, C, classes, fw, fb, labels, pooled, logits, dlogits, loss_n, correct_n, pred, dact,
+                   dfw, dfb, loss, correct, True)
+    a = act.float().requires_grad_(True)
+    w, b = fw.clone().requires_grad_(True), fb.clone().requires_grad_(True)
+    lg = F.linear(a.mean(1), w, b)
+    l = F.cross_entropy(lg, labels)
+    l.backward()
+    assert torch.allclose(logits, lg, atol=1e-3, rtol=1e-3)
+    assert abs(float(loss) - float(l)) < 1e-3
+    assert int(correct) == int((lg.argmax(1) == labels).sum())
+    assert torch.equal(pred, lg.argmax(1))
+    assert torch.allclose(dfw, w.grad, atol=1e-4, rtol=1e-3) and torch.allclose(dfb, b.grad, atol=1e-5, rtol=1e-3)
+    assert float((dact.float() - a.grad).abs().max()) <= 1e-2 * float(a.grad.abs().max()) + 1e-8
+
+
+@pytest.mark.parametrize("kind", ["adam", "sgd"])
+def test_flat_optimizer_kernel(kind):
+    from ldnn_b200.engine import FlatState, OptimConfig, Slot
+    from ldnn_b200.ops import _lib as L, native_ops as K
+    n = 4096 * 33
+    opt = OptimConfig(kind=kind, lr=3e-3, weight_decay=1e-2)
+    ref = FlatState([Slot("w", (n,), 0, n)], n, "cuda", opt)
+    ref.params.normal_()
+    p, m, v = ref.params.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    shadow = torch.zeros(n, device="cuda", dtype=torch.bfloat16)
+    for step in range(1, 6):
+        g = torch.randn(n, device="cuda")
+        ref.optimizer_step(g)
+        K.optim_step(p, g, m, v if kind == "adam" else None, shadow, n, L.make_optim(opt, step, ref.lr))
+    assert torch.allclose(p, ref.params, atol=1e-6, rtol=1e-5)
+    assert torch.equal(shadow, p.bfloat16())
+
+
+def test_im2col_stem_matches_unfold():
+    from ldnn_b200.ops import native_ops as K
+    N, C, H, W, R = 5, 3, 32, 32, 3
+    x = torch.randn(N, C, H, W, device="cuda")
+    col = torch.empty(N * H * W, 64, device="cuda", dtype=torch.bfloat16)
+    K.im2col_stem(x, col, N, C, H, W, R, 1, 1, 64)
+    ref = F.unfold(x, R, padding=1).view(N, C, R * R, H * W).permute(0, 3, 2, 1).reshape(N * H * W, R * R * C)
+    assert torch.equal(col[:, :27], ref.bfloat16()) and float(col[:, 27:].abs().max()) == 0.0

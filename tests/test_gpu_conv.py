@@ -1,0 +1,88 @@
+"""tcgen05 implicit-GEMM conv (fprop / dgrad / wgrad) vs fp32 torch conv, at every shape of the
+repo model plus ResNet-50-style shapes."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+# (N, H, W, Cin, Cout, R, stride, pad)
+ENHANCED = [
+    (64, 32, 32, 64, 128, 3, 2, 1), (64, 16, 16, 128, 128, 3, 1, 1), (64, 32, 32, 64, 128, 1, 2, 0),
+    (64, 16, 16, 128, 256, 3, 2, 1), (64, 8, 8, 256, 256, 3, 1, 1), (64, 16, 16, 128, 256, 1, 2, 0),
+    (64, 8, 8, 256, 512, 3, 2, 1), (64, 4, 4, 512, 512, 3, 1, 1), (64, 8, 8, 256, 512, 1, 2, 0),
+    (64, 4, 4, 512, 1024, 3, 2, 1), (64, 2, 2, 1024, 1024, 3, 1, 1), (64, 4, 4, 512, 1024, 1, 2, 0),
+    (64, 32, 32, 64, 64, 1, 1, 0),      # the stem after im2col (K padded to 64)
+]
+ODD = [
+    (6, 16, 16, 128, 128, 3, 1, 1),     # partial batch (upstream keeps the last short batch)
+    (5, 2, 2, 1024, 1024, 3, 1, 1),
+    (3, 14, 14, 256, 256, 3, 1, 1),     # non power-of-two image (ResNet-50 stage 4)
+    (2, 28, 28, 128, 128, 3, 2, 1),
+    (2, 56, 56, 64, 256, 1, 1, 0),
+    (2, 7, 7, 512, 2048, 1, 1, 0),
+]
+
+
+def _run(case, mode, **kw):
+    from gpu_util import fp32_mode, make_conv_case, ref_conv, ref_conv_grads, rel_err
+    from ldnn_b200.ops import native_ops as K
+    fp32_mode()
+    N, H, W, Cin, Cout, R, s, p = case
+    x, w, dy, P, Q = make_conv_case(*case)
+    if mode == K.FPROP:
+        y = torch.full((N, P, Q, Cout), float("nan"), device="cuda", dtype=torch.bfloat16)
+        K.ConvPlan(K.FPROP, N, H, W, Cin, Cout, R, s, p, x, w.view(Cout, -1), y, **kw).run()
+        torch.cuda.synchronize()
+        return rel_err(y, ref_conv(x, w, s, p))
+    dx_ref, dw_ref = ref_conv_grads(x, w, dy, s, p)
+    if mode == K.DGRAD:
+        dx = torch.zeros(N, H, W, Cin, device="cuda", dtype=torch.bfloat16)
+        K.ConvPlan(K.DGRAD, N, H, W, Cin, Cout, R, s, p, dx, w.view(Cout, -1), dy, addend=dx, accumulate=True, **kw).run()
+        torch.cuda.synchronize()
+        return rel_err(dx, dx_ref)
+    dw = torch.full((Cout, R * R * Cin), float("nan"), device="cuda", dtype=torch.float32)
+    K.ConvPlan(K.WGRAD, N, H, W, Cin, Cout, R, s, p, x, None, dy, dw=dw, **kw).run()
+    torch.cuda.synchronize()
+    return rel_err(dw.view(Cout, R, R, Cin), dw_ref)
+
+
+@pytest.mark.parametrize("case", ENHANCED + ODD)
+def test_fprop(case):
+    from ldnn_b200.ops import native_ops as K
+    assert _run(case, K.FPROP) < 1.5e-2
+
+
+@pytest.mark.parametrize("case", [c for c in ENHANCED + ODD])
+def test_dgrad(case):
+    from ldnn_b200.ops import native_ops as K
+    assert _run(case, K.DGRAD) < 1.5e-2
+
+
+@pytest.mark.parametrize("case", ENHANCED + ODD)
+def test_wgrad(case):
+    from ldnn_b200.ops import native_ops as K
+    assert _run(case, K.WGRAD) < 5e-3
+
+
+@pytest.mark.parametrize("splits", [1, 2, 5])
+@pytest.mark.parametrize("block_n", [64, 128, 256])
+def test_tile_and_split_variants(splits, block_n):
+    from ldnn_b200.ops import native_ops as K
+    case = (8, 8, 8, 256, 256, 3, 1, 1)
+    assert _run(case, K.FPROP, splits=splits, block_n=block_n) < 1.5e-2
+    assert _run(case, K.DGRAD, splits=splits, block_n=block_n) < 1.5e-2
+    assert _run(case, K.WGRAD, splits=splits, block_n=block_n) < 5e-3
+
+
+def test_split_k_is_deterministic_and_reusable():
+    from gpu_util import make_conv_case
+    from ldnn_b200.ops import native_ops as K
+    N, H, W, Cin, Cout, R, s, p = case = (64, 2, 2, 1024, 1024, 3, 1, 1)
+    x, w, dy, P, Q = make_conv_case(*case)
+    y = torch.empty(N, P, Q, Cout, device="cuda", dtype=torch.bfloat16)
+    plan = K.ConvPlan(K.FPROP, N, H, W, Cin, Cout, R, s, p, x, w.view(Cout, -1), y)
+    assert plan.scratch_bytes > 0
+    plan.run(); torch.cuda.synchronize(); y0 = y.clone()
+    for _ in range(3):
+        y.zero_(); plan.run(); torch.cuda.synchronize()
+        assert torch.equal(y, y0)
