@@ -165,9 +165,16 @@ class Engine:
                 self.import_tensor(f.v, s.key, sd["v"][s.key])
 
 
+def canonical_device(device) -> torch.device:
+    d = torch.device(device)
+    if d.type == "cuda" and d.index is None:
+        d = torch.device("cuda", torch.cuda.current_device())
+    return d
+
+
 class TorchEngine(Engine):
     def __init__(self, spec: NetSpec, device, opt: OptimConfig, init: bool = True):
-        self.spec, self.device = spec, torch.device(device)
+        self.spec, self.device = spec, canonical_device(device)
         self.model = SpecNet(spec)
         if init:
             xavier_init_(self.model)

@@ -23,7 +23,7 @@ from typing import Dict, List, Optional, Tuple
 
 import torch
 
-from ..engine import ALIGN, Engine, FlatState, OptimConfig, Slot
+from ..engine import ALIGN, Engine, FlatState, OptimConfig, Slot, canonical_device
 from ..ops import _lib as L
 from ..ops import native_ops as K
 from .spec import ConvBN, Head, MaxPool, NetSpec
@@ -56,7 +56,7 @@ class NativeEngine(Engine):
                  rank: int = 0, init: bool = True, use_graph: bool = True):
         if not L.available():
             raise L.LdnnError("libldnn_b200.so is not built; run `python -m ldnn_b200.build`")
-        self.spec, self.device, self.max_batch = spec, torch.device(device), batch_size
+        self.spec, self.device, self.max_batch = spec, canonical_device(device), batch_size
         self.use_graph = use_graph
         torch.cuda.set_device(self.device)
         # ---- geometry ------------------------------------------------------------
