@@ -438,3 +438,68 @@ extern "C" int ldnn_maxpool_bwd(const void* x, const void* y, const void* dy, vo
   LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
+
+// ------------------------------------------------------------------ allocation-free BN statistics
+// Some users of this library cannot give the BN-statistics kernel a workspace, and cannot obtain
+// one: code that runs as a plug-in or custom op inside a host which has handed the whole GPU to its
+// own caching allocator (so a cudaMalloc from here fails, or fragments the host's pool), and loops
+// that must never hit cudaMalloc/cudaFree because those calls synchronise the whole device.
+// For them the per-CTA partial sums and the arrival ticket live in the fixed array below, which
+// every GPU that loads this library keeps resident until the process exits.
+//
+// Capacity: chunks * 2 * C floats must fit in kNoAllocPartialFloats (1 MiB: e.g. 128 chunks at
+// C = 1024, or 64 chunks at C = 2048).  Larger requests are refused; use ldnn_bn_fwd_stats with a
+// caller-owned workspace instead.
+constexpr size_t kNoAllocTicketWords = 64;                 // 256 B header: word 0 is the ticket
+constexpr size_t kNoAllocPartialFloats = 262144;           // 1 MiB of partial sums
+static __device__ __align__(256) float g_bn_noalloc_scratch[kNoAllocTicketWords + kNoAllocPartialFloats];
+
+namespace ldnn {
+// The array's name is only a host-side handle; the device address is looked up once per device
+// (with that device current) and cached here.
+static float* g_bn_noalloc_ptr[64] = {nullptr};
+
+static int bn_noalloc_scratch(float** out) {
+  int dev = -1;
+  LDNN_CUDA(cudaGetDevice(&dev));
+  LDNN_ARG(dev >= 0 && dev < 64, "device ordinal %d out of range", dev);
+  if (g_bn_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    LDNN_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_bn_noalloc_scratch));
+    LDNN_ARG(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    g_bn_noalloc_ptr[dev] = p;
+  }
+  *out = g_bn_noalloc_ptr[dev];
+  return LDNN_OK;
+}
+}  // namespace ldnn
+
+extern "C" int ldnn_bn_fwd_stats_noalloc(const void* y, int M, int C, int chunks, const float* gamma,
+                                         const float* beta, float* running_mean, float* running_var,
+                                         long long* nbt, float* save_mean, float* save_invstd, float* scale,
+                                         float* shift, float eps, float momentum, void* stream) {
+  LDNN_ARG(C % 8 == 0 && C / 8 <= kBnThreads, "bn: C=%d unsupported (need C%%8==0, C<=2048)", C);
+  LDNN_ARG(chunks >= 1, "bn: chunks");
+  const size_t need = (size_t)chunks * 2 * (size_t)C;
+  LDNN_ARG(need <= kNoAllocPartialFloats,
+           "bn_fwd_stats_noalloc: chunks*2*C = %zu floats exceeds the built-in scratch of %zu floats (1 MiB); "
+           "lower `chunks` or call ldnn_bn_fwd_stats with your own workspace", need, kNoAllocPartialFloats);
+  float* base = nullptr;
+  int rc = bn_noalloc_scratch(&base);
+  if (rc) return rc;
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(base);
+  float* partial = base + kNoAllocTicketWords;
+  cudaStream_t st = (cudaStream_t)stream;
+  // The array keeps whatever the previous call left.  Partials are fully overwritten before they
+  // are read; the ticket must start at zero, so it is cleared in stream order.
+  LDNN_CUDA(cudaMemsetAsync(ticket, 0, kNoAllocTicketWords * sizeof(unsigned int), st));
+  const int rows = (M + chunks - 1) / chunks;
+  const int lanes = kBnThreads / (C / 8);
+  const size_t smem = (size_t)lanes * 2 * C * sizeof(float);
+  bn_stats_kernel<<<chunks, kBnThreads, smem, st>>>((const __nv_bfloat16*)y, partial, ticket, M, C, rows, gamma, beta,
+                                                   running_mean, running_var, nbt, save_mean, save_invstd, scale,
+                                                   shift, eps, momentum);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}

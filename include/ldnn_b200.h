@@ -59,6 +59,22 @@ int ldnn_bn_fwd_stats(const void* y, int M, int C, int chunks, float* partial, u
                       const float* gamma, const float* beta, float* running_mean, float* running_var,
                       long long* num_batches_tracked, float* save_mean, float* save_invstd, float* scale,
                       float* shift, float eps, float momentum, void* stream);
+/* Same computation as ldnn_bn_fwd_stats, for callers that cannot allocate device memory and have no
+ * workspace to pass: plug-ins / custom ops living inside a host whose allocator owns the whole GPU,
+ * and steady-state loops that must not call cudaMalloc/cudaFree (both synchronise the device).
+ * The partial sums and the ticket live in a fixed 1 MiB (+256 B) array inside the library, resident on
+ * every GPU that loads it until process exit.  Limits: chunks*2*C <= 262144 floats, otherwise the call
+ * is refused with an error.  It calls no cudaMalloc/cudaFree and no allocating library routine.
+ * The first call on each device looks up the array's device address (one-time set-up, with that
+ * device current): make that first call before any stream capture begins.  Every call on a device
+ * shares the one array, and the array keeps the previous call's contents (the ticket is cleared in
+ * stream order at the start of each call): two calls that overlap on the GPU race with each other —
+ * keep them on one stream or order them yourself.
+ * This entry point has no counterpart in the reference. */
+int ldnn_bn_fwd_stats_noalloc(const void* y, int M, int C, int chunks, const float* gamma, const float* beta,
+                              float* running_mean, float* running_var, long long* num_batches_tracked,
+                              float* save_mean, float* save_invstd, float* scale, float* shift, float eps,
+                              float momentum, void* stream);
 /* eval mode: scale/shift from the running statistics */
 int ldnn_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
                         float* scale, float* shift, int C, float eps, void* stream);
