@@ -16,49 +16,84 @@ extern std::atomic<unsigned long long> g_launches;
 
 constexpr int kBnThreads = 256;
 
-// thread layout shared by the reduction kernels: 8 channels per thread, C/8 channel groups,
-// 256/(C/8) pixel lanes per CTA.
+// Thread layout shared by the reduction kernels: a CTA owns a slab of 64 channels (blockIdx.x) and a
+// chunk of rows (blockIdx.y); thread = 8 consecutive channels (one 16-byte load) x 32 row lanes, so
+// layers with many channels and few pixels (layer3/4) still spread over many CTAs.
+constexpr int kSlab = 64;
 struct Lanes {
-  int c8, lanes, cg, pl;
-  __device__ Lanes(int C) {
-    c8 = C >> 3;
-    lanes = kBnThreads / c8;
-    cg = threadIdx.x % c8;
-    pl = threadIdx.x / c8;
+  int cg, pl, c0;
+  __device__ Lanes() {
+    cg = threadIdx.x & 7;
+    pl = threadIdx.x >> 3;
+    c0 = blockIdx.x * kSlab + cg * 8;
   }
 };
+constexpr int kRowLanes = kBnThreads / 8;   // 32
 
-// Block-level fold of per-thread (a[8], b[8]) over pixel lanes -> partial[chunk][2][C].
+// Block-level fold of per-thread (a[8], b[8]) over the 32 row lanes -> partial[chunk][2][C] (this slab).
 __device__ __forceinline__ void fold_to_partial(const Lanes& L, float (&a)[8], float (&b)[8], float* smem,
                                                 float* partial, int C) {
-  // smem layout: [lanes][2][C]
-  if (L.pl < L.lanes) {
+  // smem layout: [lanes][2][64]
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      smem[(L.pl * 2 + 0) * C + L.cg * 8 + i] = a[i];
-      smem[(L.pl * 2 + 1) * C + L.cg * 8 + i] = b[i];
-    }
+  for (int i = 0; i < 8; ++i) {
+    smem[(L.pl * 2 + 0) * kSlab + L.cg * 8 + i] = a[i];
+    smem[(L.pl * 2 + 1) * kSlab + L.cg * 8 + i] = b[i];
   }
   __syncthreads();
-  for (int idx = threadIdx.x; idx < 2 * C; idx += kBnThreads) {
+  if (threadIdx.x < 2 * kSlab) {
+    const int which = threadIdx.x / kSlab, c = threadIdx.x % kSlab;
     float s = 0.f;
-    for (int l = 0; l < L.lanes; ++l) s += smem[l * 2 * C + idx];
-    partial[(size_t)blockIdx.x * 2 * C + idx] = s;
+#pragma unroll 8
+    for (int l = 0; l < kRowLanes; ++l) s += smem[(l * 2 + which) * kSlab + c];
+    partial[((size_t)blockIdx.y * 2 + which) * C + blockIdx.x * kSlab + c] = s;
   }
 }
 
+// "Last CTA" election.  One fence per CTA (thread 0, after the CTA barrier) publishes the whole CTA's
+// partials before the ticket; the elected CTA fences once more before reading the others' partials.
 __device__ __forceinline__ bool take_ticket_last(unsigned int* ticket) {
   __shared__ unsigned int s_last;
-  __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
-    unsigned int old = atomicAdd(ticket, 1u);
-    s_last = (old == gridDim.x - 1) ? 1u : 0u;
-    if (s_last) *ticket = 0;
+    __threadfence();
+    const unsigned int old = atomicAdd(ticket, 1u);
+    s_last = (old == gridDim.x * gridDim.y - 1) ? 1u : 0u;
+    if (s_last) { *ticket = 0; __threadfence(); }
   }
   __syncthreads();
-  if (s_last) __threadfence();
   return s_last != 0;
+}
+
+// Last-CTA fold: out[0..2C) = sum over chunks of partial[chunk][0..2C), into smem.
+// 2C columns x S slices of the chunk range run in parallel; every slice sums its chunks in order
+// and the slices are combined in order, so the result does not depend on scheduling.
+__device__ __forceinline__ void fold_partials(const float* __restrict__ partial, float* smem, int C, int chunks) {
+  const int cols = 2 * C;
+  const int S = max(1, kBnThreads / cols);              // slices (cols < 256 only)
+  float* stage = smem + cols;                           // [S][cols] staging behind the result
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < cols * S; idx += kBnThreads) {
+    const int col = idx % cols, sl = idx / cols;
+    const int k0 = (int)((long long)chunks * sl / S), k1 = (int)((long long)chunks * (sl + 1) / S);
+    float acc = 0.f;
+    int k = k0;
+    for (; k + 8 <= k1; k += 8) {
+      float t[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t[j] = __ldcg(&partial[(size_t)(k + j) * cols + col]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc += t[j];
+    }
+    for (; k < k1; ++k) acc += __ldcg(&partial[(size_t)k * cols + col]);
+    stage[sl * cols + col] = acc;
+  }
+  __syncthreads();
+  for (int col = threadIdx.x; col < cols; col += kBnThreads) {
+    float acc = 0.f;
+    for (int sl = 0; sl < S; ++sl) acc += stage[sl * cols + col];
+    smem[col] = acc;
+  }
+  __syncthreads();
 }
 
 // ------------------------------------------------------------------ forward stats
@@ -68,30 +103,26 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* __restrict__ partial
                 float* running_mean, float* running_var, long long* nbt, float* save_mean, float* save_invstd,
                 float* scale, float* shift, float eps, float momentum) {
   extern __shared__ float smem[];
-  Lanes L(C);
+  Lanes L;
   float s[8], q[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) { s[i] = 0.f; q[i] = 0.f; }
-  const int r0 = blockIdx.x * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
-  if (L.pl < L.lanes) {
-    for (int r = r0 + L.pl; r < r1; r += L.lanes) {
-      const uint4 u = *reinterpret_cast<const uint4*>(y + (size_t)r * C + L.cg * 8);
-      float f[8];
-      bf16x8_to_float(u, f);
+  const int r0 = blockIdx.y * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
+#pragma unroll 4
+  for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
+    const uint4 u = *reinterpret_cast<const uint4*>(y + (size_t)r * C + L.c0);
+    float f[8];
+    bf16x8_to_float(u, f);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] += f[i] * f[i]; }
-    }
+    for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] += f[i] * f[i]; }
   }
   fold_to_partial(L, s, q, smem, partial, C);
   if (!take_ticket_last(ticket)) return;
-  // ---- last CTA: finalize ----
+  // ---- last CTA: finalize (all 256 threads fold the partials; fixed order => deterministic) ----
+  fold_partials(partial, smem, C, gridDim.y);
   const float inv_m = 1.f / (float)M;
   for (int c = threadIdx.x; c < C; c += kBnThreads) {
-    float sum = 0.f, sq = 0.f;
-    for (int k = 0; k < (int)gridDim.x; ++k) {
-      sum += __ldcg(&partial[(size_t)k * 2 * C + c]);
-      sq += __ldcg(&partial[(size_t)k * 2 * C + C + c]);
-    }
+    const float sum = smem[c], sq = smem[C + c];
     const float mean = sum * inv_m;
     const float var = fmaxf(sq * inv_m - mean * mean, 0.f);
     const float invstd = rsqrtf(var + eps);
@@ -156,39 +187,32 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16
                      const float* __restrict__ invstd, float* __restrict__ partial, unsigned int* ticket, int M, int C,
                      int rows_per_chunk, int relu, float* dgamma, float* dbeta) {
   extern __shared__ float smem[];
-  Lanes L(C);
+  Lanes L;
   float a[8], b[8], mu[8], is[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) { a[i] = 0.f; b[i] = 0.f; }
-  if (L.pl < L.lanes) {
+  for (int i = 0; i < 8; ++i) { a[i] = 0.f; b[i] = 0.f; mu[i] = mean[L.c0 + i]; is[i] = invstd[L.c0 + i]; }
+  const int r0 = blockIdx.y * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
+#pragma unroll 2
+  for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
+    const size_t off = (size_t)r * C + L.c0;
+    float g[8], yy[8];
+    bf16x8_to_float(*reinterpret_cast<const uint4*>(dout + off), g);
+    bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), yy);
+    if (relu) {
+      float o[8];
+      bf16x8_to_float(*reinterpret_cast<const uint4*>(outp + off), o);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { mu[i] = mean[L.cg * 8 + i]; is[i] = invstd[L.cg * 8 + i]; }
-    const int r0 = blockIdx.x * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
-    for (int r = r0 + L.pl; r < r1; r += L.lanes) {
-      const size_t off = (size_t)r * C + L.cg * 8;
-      float g[8], yy[8];
-      bf16x8_to_float(*reinterpret_cast<const uint4*>(dout + off), g);
-      bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), yy);
-      if (relu) {
-        float o[8];
-        bf16x8_to_float(*reinterpret_cast<const uint4*>(outp + off), o);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) g[i] = (o[i] > 0.f) ? g[i] : 0.f;
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) { a[i] += g[i]; b[i] += g[i] * (yy[i] - mu[i]) * is[i]; }
+      for (int i = 0; i < 8; ++i) g[i] = (o[i] > 0.f) ? g[i] : 0.f;
     }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { a[i] += g[i]; b[i] += g[i] * (yy[i] - mu[i]) * is[i]; }
   }
   fold_to_partial(L, a, b, smem, partial, C);
   if (!take_ticket_last(ticket)) return;
+  fold_partials(partial, smem, C, gridDim.y);
   for (int c = threadIdx.x; c < C; c += kBnThreads) {
-    float sa = 0.f, sb = 0.f;
-    for (int k = 0; k < (int)gridDim.x; ++k) {
-      sa += __ldcg(&partial[(size_t)k * 2 * C + c]);
-      sb += __ldcg(&partial[(size_t)k * 2 * C + C + c]);
-    }
-    dbeta[c] = sa;
-    dgamma[c] = sb;
+    dbeta[c] = smem[c];
+    dgamma[c] = smem[C + c];
   }
 }
 
@@ -232,6 +256,162 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16*
       const float is = invstd[c];
       const float xh = (yy[k] - mean[c]) * is;
       o8[k] = gamma[c] * is * (g[k] - dbeta[c] * inv_m - xh * dgamma[c] * inv_m);
+    }
+    reinterpret_cast<uint4*>(dy_raw)[i] = float_to_bf16x8(o8);
+  }
+}
+
+// ------------------------------------------------------------------ "sums" variants (fast path)
+// The conv epilogue already accumulated per-channel sum / sum-of-squares (conv_gemm.cuh), so the BN
+// forward is ONE kernel: every CTA derives scale/shift for all channels into smem (CTA 0 also writes
+// save_mean/save_invstd and the running statistics), then streams normalize + residual + ReLU.
+// Backward likewise: `reduce` accumulates (sum dy, sum dy*xhat) with red.add (no ticket chain) and
+// `apply` derives dgamma/dbeta + the per-channel coefficients in its prologue.
+__global__ void __launch_bounds__(256)
+bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ sums,
+                     const float* __restrict__ gamma, const float* __restrict__ beta, float* running_mean,
+                     float* running_var, long long* nbt, float* save_mean, float* save_invstd,
+                     const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out, long long total8, int C,
+                     int M, int relu, int training, float eps, float momentum) {
+  extern __shared__ float sm[];
+  float* s_scale = sm;
+  float* s_shift = sm + C;
+  const float inv_m = 1.f / (float)M;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float mean, var;
+    if (training) {
+      mean = sums[c] * inv_m;
+      var = fmaxf(sums[C + c] * inv_m - mean * mean, 0.f);
+    } else {
+      mean = running_mean[c];
+      var = running_var[c];
+    }
+    const float invstd = rsqrtf(var + eps);
+    const float g = gamma[c];
+    s_scale[c] = g * invstd;
+    s_shift[c] = beta[c] - mean * g * invstd;
+    if (training && blockIdx.x == 0) {
+      save_mean[c] = mean;
+      save_invstd[c] = invstd;
+      const float unbiased = (M > 1) ? var * (float)M / (float)(M - 1) : var;
+      running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+    }
+  }
+  if (training && blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
+  __syncthreads();
+  const int c8 = C >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total8;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % c8) * 8;
+    float f[8];
+    bf16x8_to_float(reinterpret_cast<const uint4*>(y)[i], f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = f[k] * s_scale[c0 + k] + s_shift[c0 + k];
+    if (res) {
+      float r[8];
+      bf16x8_to_float(reinterpret_cast<const uint4*>(res)[i], r);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] += r[k];
+    }
+    if (relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+    }
+    reinterpret_cast<uint4*>(out)[i] = float_to_bf16x8(f);
+  }
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_atomic_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
+                            const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+                            const float* __restrict__ invstd, float* __restrict__ sums, int M, int C,
+                            int rows_per_chunk, int relu) {
+  __shared__ float smem[kRowLanes * 2 * kSlab];
+  Lanes L;
+  float a[8], b[8], mu[8], is[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { a[i] = 0.f; b[i] = 0.f; mu[i] = mean[L.c0 + i]; is[i] = invstd[L.c0 + i]; }
+  const int r0 = blockIdx.y * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
+#pragma unroll 2
+  for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
+    const size_t off = (size_t)r * C + L.c0;
+    float g[8], yy[8];
+    bf16x8_to_float(*reinterpret_cast<const uint4*>(dout + off), g);
+    bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), yy);
+    if (relu) {
+      float o[8];
+      bf16x8_to_float(*reinterpret_cast<const uint4*>(outp + off), o);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) g[i] = (o[i] > 0.f) ? g[i] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { a[i] += g[i]; b[i] += g[i] * (yy[i] - mu[i]) * is[i]; }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    smem[(L.pl * 2 + 0) * kSlab + L.cg * 8 + i] = a[i];
+    smem[(L.pl * 2 + 1) * kSlab + L.cg * 8 + i] = b[i];
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * kSlab) {
+    const int which = threadIdx.x / kSlab, c = threadIdx.x % kSlab;
+    float t = 0.f;
+#pragma unroll 8
+    for (int l = 0; l < kRowLanes; ++l) t += smem[(l * 2 + which) * kSlab + c];
+    atomicAdd(&sums[(size_t)which * C + blockIdx.x * kSlab + c], t);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_sums_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
+                         const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+                         const float* __restrict__ invstd, const float* __restrict__ gamma,
+                         const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy_raw,
+                         __nv_bfloat16* __restrict__ dres, float* dgamma, float* dbeta, long long total8, int C,
+                         int relu, int res_accumulate, float inv_m) {
+  extern __shared__ float sm[];
+  float* s_mean = sm;            // mean
+  float* s_is = sm + C;          // invstd
+  float* s_k = sm + 2 * C;       // gamma*invstd
+  float* s_b = sm + 3 * C;       // dbeta/M
+  float* s_g = sm + 4 * C;       // dgamma/M
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float is = invstd[c], db = sums[c], dg = sums[C + c];
+    s_mean[c] = mean[c]; s_is[c] = is; s_k[c] = gamma[c] * is; s_b[c] = db * inv_m; s_g[c] = dg * inv_m;
+    if (blockIdx.x == 0) { dbeta[c] = db; dgamma[c] = dg; }
+  }
+  __syncthreads();
+  const int c8 = C >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total8;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % c8) * 8;
+    float g[8], yy[8];
+    bf16x8_to_float(reinterpret_cast<const uint4*>(dout)[i], g);
+    bf16x8_to_float(reinterpret_cast<const uint4*>(y)[i], yy);
+    if (relu) {
+      float o[8];
+      bf16x8_to_float(reinterpret_cast<const uint4*>(outp)[i], o);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = (o[k] > 0.f) ? g[k] : 0.f;
+    }
+    if (dres) {
+      if (res_accumulate) {
+        float r[8], t[8];
+        bf16x8_to_float(reinterpret_cast<const uint4*>(dres)[i], r);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t[k] = r[k] + g[k];
+        reinterpret_cast<uint4*>(dres)[i] = float_to_bf16x8(t);
+      } else {
+        reinterpret_cast<uint4*>(dres)[i] = float_to_bf16x8(g);
+      }
+    }
+    float o8[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c0 + k;
+      const float xh = (yy[k] - s_mean[c]) * s_is[c];
+      o8[k] = s_k[c] * (g[k] - s_b[c] - xh * s_g[c]);
     }
     reinterpret_cast<uint4*>(dy_raw)[i] = float_to_bf16x8(o8);
   }
@@ -330,6 +510,12 @@ __global__ void maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __
   }
 }
 
+static size_t bn_smem_bytes(int C, int lanes) {
+  const size_t fold = (size_t)lanes * 2 * kSlab;                               // per-lane partials of one slab
+  const size_t fin = (size_t)2 * C + std::max<size_t>(kBnThreads, (size_t)2 * C);  // result + slice staging
+  return std::max(fold, fin) * sizeof(float);
+}
+
 static int grid_for(long long work, int threads, int max_blocks = 148 * 8) {
   long long b = (work + threads - 1) / threads;
   return (int)std::max(1LL, std::min<long long>(b, max_blocks));
@@ -344,12 +530,12 @@ extern "C" int ldnn_bn_fwd_stats(const void* y, int M, int C, int chunks, float*
                                  const float* gamma, const float* beta, float* running_mean, float* running_var,
                                  long long* nbt, float* save_mean, float* save_invstd, float* scale, float* shift,
                                  float eps, float momentum, void* stream) {
-  LDNN_ARG(C % 8 == 0 && C / 8 <= kBnThreads, "bn: C=%d unsupported (need C%%8==0, C<=2048)", C);
+  LDNN_ARG(C % kSlab == 0 && C <= 2048, "bn: C=%d unsupported (need C%%64==0, C<=2048)", C);
   LDNN_ARG(chunks >= 1, "bn: chunks");
   const int rows = (M + chunks - 1) / chunks;
-  const int lanes = kBnThreads / (C / 8);
-  const size_t smem = (size_t)lanes * 2 * C * sizeof(float);
-  bn_stats_kernel<<<chunks, kBnThreads, smem, (cudaStream_t)stream>>>(
+  const int lanes = kRowLanes;
+  const size_t smem = bn_smem_bytes(C, lanes);
+  bn_stats_kernel<<<dim3(C / kSlab, chunks), kBnThreads, smem, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)y, partial, ticket, M, C, rows, gamma, beta, running_mean, running_var, nbt, save_mean,
       save_invstd, scale, shift, eps, momentum);
   COUNT_LAUNCH();
@@ -379,11 +565,11 @@ extern "C" int ldnn_bn_fwd_apply(const void* y, const float* scale, const float*
 extern "C" int ldnn_bn_bwd_reduce(const void* dout, const void* out, const void* y, const float* save_mean,
                                   const float* save_invstd, float* partial, unsigned int* ticket, int M, int C,
                                   int chunks, int relu, float* dgamma, float* dbeta, void* stream) {
-  LDNN_ARG(C % 8 == 0 && C / 8 <= kBnThreads, "bn: C=%d unsupported", C);
+  LDNN_ARG(C % kSlab == 0 && C <= 2048, "bn: C=%d unsupported (need C%%64==0, C<=2048)", C);
   const int rows = (M + chunks - 1) / chunks;
-  const int lanes = kBnThreads / (C / 8);
-  const size_t smem = (size_t)lanes * 2 * C * sizeof(float);
-  bn_bwd_reduce_kernel<<<chunks, kBnThreads, smem, (cudaStream_t)stream>>>(
+  const int lanes = kRowLanes;
+  const size_t smem = bn_smem_bytes(C, lanes);
+  bn_bwd_reduce_kernel<<<dim3(C / kSlab, chunks), kBnThreads, smem, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, partial,
       ticket, M, C, rows, relu, dgamma, dbeta);
   COUNT_LAUNCH();
@@ -399,6 +585,50 @@ extern "C" int ldnn_bn_bwd_apply(const void* dout, const void* out, const void* 
   bn_bwd_apply_kernel<<<grid_for(total8, 256), 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, gamma,
       dgamma, dbeta, (__nv_bfloat16*)dy_raw, (__nv_bfloat16*)dres, total8, C, relu, res_accumulate, 1.f / (float)M);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_bn_fwd_apply_sums(const void* y, const float* sums, const float* gamma, const float* beta,
+                                      float* running_mean, float* running_var, long long* nbt, float* save_mean,
+                                      float* save_invstd, const void* residual, void* out, int M, int C, int relu,
+                                      int training, float eps, float momentum, void* stream) {
+  LDNN_ARG(C % 8 == 0 && C <= 4096, "bn: C=%d unsupported", C);
+  const long long total8 = (long long)M * C / 8;
+  const int blocks = (int)std::max(1LL, std::min<long long>((total8 + 1023) / 1024, 148 * 4));
+  bn_apply_sums_kernel<<<blocks, 256, 2 * C * sizeof(float), (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)y, sums, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd,
+      (const __nv_bfloat16*)residual, (__nv_bfloat16*)out, total8, C, M, relu, training, eps, momentum);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_bn_bwd_reduce_sums(const void* dout, const void* out, const void* y, const float* save_mean,
+                                       const float* save_invstd, float* sums, int M, int C, int chunks, int relu,
+                                       void* stream) {
+  LDNN_ARG(C % kSlab == 0, "bn: C=%d unsupported (need C%%64==0)", C);
+  const int rows = (M + chunks - 1) / chunks;
+  bn_bwd_reduce_atomic_kernel<<<dim3(C / kSlab, chunks), kBnThreads, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, sums, M,
+      C, rows, relu);
+  COUNT_LAUNCH();
+  LDNN_CUDA(cudaGetLastError());
+  return LDNN_OK;
+}
+
+extern "C" int ldnn_bn_bwd_apply_sums(const void* dout, const void* out, const void* y, const float* save_mean,
+                                      const float* save_invstd, const float* gamma, const float* sums, void* dy_raw,
+                                      void* dres, float* dgamma, float* dbeta, int M, int C, int relu,
+                                      int res_accumulate, void* stream) {
+  LDNN_ARG(C % 8 == 0 && C <= 2048, "bn: C=%d unsupported", C);
+  const long long total8 = (long long)M * C / 8;
+  const int blocks = (int)std::max(1LL, std::min<long long>((total8 + 1023) / 1024, 148 * 4));
+  bn_bwd_apply_sums_kernel<<<blocks, 256, 5 * C * sizeof(float), (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, gamma,
+      sums, (__nv_bfloat16*)dy_raw, (__nv_bfloat16*)dres, dgamma, dbeta, total8, C, relu, res_accumulate,
+      1.f / (float)M);
   COUNT_LAUNCH();
   LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
@@ -478,7 +708,7 @@ extern "C" int ldnn_bn_fwd_stats_noalloc(const void* y, int M, int C, int chunks
                                          const float* beta, float* running_mean, float* running_var,
                                          long long* nbt, float* save_mean, float* save_invstd, float* scale,
                                          float* shift, float eps, float momentum, void* stream) {
-  LDNN_ARG(C % 8 == 0 && C / 8 <= kBnThreads, "bn: C=%d unsupported (need C%%8==0, C<=2048)", C);
+  LDNN_ARG(C % kSlab == 0 && C <= 2048, "bn: C=%d unsupported (need C%%64==0, C<=2048)", C);
   LDNN_ARG(chunks >= 1, "bn: chunks");
   const size_t need = (size_t)chunks * 2 * (size_t)C;
   LDNN_ARG(need <= kNoAllocPartialFloats,
@@ -494,9 +724,9 @@ extern "C" int ldnn_bn_fwd_stats_noalloc(const void* y, int M, int C, int chunks
   // are read; the ticket must start at zero, so it is cleared in stream order.
   LDNN_CUDA(cudaMemsetAsync(ticket, 0, kNoAllocTicketWords * sizeof(unsigned int), st));
   const int rows = (M + chunks - 1) / chunks;
-  const int lanes = kBnThreads / (C / 8);
-  const size_t smem = (size_t)lanes * 2 * C * sizeof(float);
-  bn_stats_kernel<<<chunks, kBnThreads, smem, st>>>((const __nv_bfloat16*)y, partial, ticket, M, C, rows, gamma, beta,
+  const int lanes = kRowLanes;
+  const size_t smem = bn_smem_bytes(C, lanes);
+  bn_stats_kernel<<<dim3(C / kSlab, chunks), kBnThreads, smem, st>>>((const __nv_bfloat16*)y, partial, ticket, M, C, rows, gamma, beta,
                                                    running_mean, running_var, nbt, save_mean, save_invstd, scale,
                                                    shift, eps, momentum);
   COUNT_LAUNCH();

@@ -78,6 +78,7 @@ struct Plan {
   const void* addend;
   float* scratch;
   unsigned int* tickets;
+  float* stats;
 };
 
 static void pixel_box(int Wd, int Hd, int Nd, int target, ConvParams& p) {
@@ -120,6 +121,7 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   plan.out = (d.mode == MODE_FPROP) ? d.y : (d.mode == MODE_DGRAD ? const_cast<void*>(d.x) : d.dw);
   plan.addend = d.addend ? d.addend : plan.out;
   plan.scratch = d.scratch; plan.tickets = d.tickets;
+  plan.stats = (d.mode == MODE_FPROP) ? d.bn_sums : nullptr;
 
   const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(d.x);
   const __nv_bfloat16* yb = reinterpret_cast<const __nv_bfloat16*>(d.y);
@@ -282,7 +284,7 @@ static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
   }
   conv_gemm_kernel<MODE, BN><<<L.grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(
       L.maps, L.p, pl.out, pl.addend, pl.scratch ? pl.scratch + L.scratch_off : nullptr,
-      pl.tickets ? pl.tickets + L.ticket_off : nullptr);
+      pl.tickets ? pl.tickets + L.ticket_off : nullptr, pl.stats);
   g_launches.fetch_add(1, std::memory_order_relaxed);
   LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;

@@ -67,7 +67,8 @@ struct ConvCfg {
 template <int MODE, int BLOCK_N>
 __global__ void __launch_bounds__(192, 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void* __restrict__ out,
-                 const void* __restrict__ addend, float* __restrict__ scratch, unsigned int* __restrict__ tickets) {
+                 const void* __restrict__ addend, float* __restrict__ scratch, unsigned int* __restrict__ tickets,
+                 float* __restrict__ stats) {
   using Cfg = ConvCfg<BLOCK_N>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -229,6 +230,42 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
       }
     };
 
+    // ---- fused BN statistics (fprop): per-channel sum / sum of squares of the fp32 accumulators ----
+    // Warp transpose-reduce (recursive halving, 31 shuffles per quantity): afterwards lane L holds the
+    // total of column col0+L over this warp's 32 rows.  The 4 epilogue warps meet in (now idle)
+    // pipeline smem and 2*BLOCK_N red.add's per CTA accumulate into stats[2][Cout].
+    float* red = reinterpret_cast<float*>(smem);          // [BLOCK_N/32][4][2][32]
+    const bool do_stats = (MODE == MODE_FPROP) && (stats != nullptr);
+    auto col_stats = [&](int col0, const float (&v)[32]) {
+      float a[32], b[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) { a[i] = row_ok ? v[i] : 0.f; b[i] = a[i] * a[i]; }
+      const uint32_t lane = lane_id();
+#pragma unroll
+      for (int off = 16; off >= 1; off >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+          const float keep_a = upper ? a[i + off] : a[i], send_a = upper ? a[i] : a[i + off];
+          const float keep_b = upper ? b[i + off] : b[i], send_b = upper ? b[i] : b[i + off];
+          a[i] = keep_a + __shfl_xor_sync(0xffffffffu, send_a, off);
+          b[i] = keep_b + __shfl_xor_sync(0xffffffffu, send_b, off);
+        }
+      }
+      float* dst = red + ((col0 >> 5) * 4 + (warp - 2)) * 64;
+      dst[lane] = a[0];
+      dst[32 + lane] = b[0];
+    };
+    auto flush_stats = [&]() {
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+      for (int idx = et; idx < 2 * BLOCK_N; idx += 128) {
+        const int which = idx / BLOCK_N, col = idx % BLOCK_N;
+        const float* src = red + (col >> 5) * 4 * 64 + which * 32 + (col & 31);
+        const float t = src[0] + src[64] + src[128] + src[192];
+        atomicAdd(&stats[(size_t)which * p.n_total + n0 + col], t);
+      }
+    };
+
     const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
     if (p.splits == 1) {
 #pragma unroll 1
@@ -240,7 +277,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
         emit(c, v);
+        if (do_stats) col_stats(c, v);
       }
+      if (do_stats) flush_stats();
     } else {
       // ---- split-K: park the partial tile, take a ticket, last arriver reduces ----
       const int tiles_n = gridDim.y;
@@ -258,22 +297,40 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
           part[(c / 4 + i) * 128 + row] = make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]),
                                                       __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
       }
-      __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (et == 0) {
+        __threadfence();                       // one fence per CTA publishes every epilogue thread's partial
         const unsigned int old = atomicAdd(&tickets[tile_lin], 1u);
-        *last_flag = (old == static_cast<unsigned int>(p.splits - 1)) ? 1u : 0u;
+        const unsigned int last = (old == static_cast<unsigned int>(p.splits - 1)) ? 1u : 0u;
+        if (last) __threadfence();
+        *last_flag = last;
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (*last_flag) {
-        __threadfence();
         const float4* base = reinterpret_cast<const float4*>(scratch) + tile_lin * p.splits * (BLOCK_N / 4) * 128;
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N; c += 32) {
           float v[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = 0.f;
-          for (int s = 0; s < p.splits; ++s) {
+          // fixed summation order; 4 splits x 8 vectors in flight per thread
+          int s = 0;
+          for (; s + 4 <= p.splits; s += 4) {
+            float4 t[4][8];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const float4* ps = base + (long long)(s + u) * (BLOCK_N / 4) * 128;
+#pragma unroll
+              for (int i = 0; i < 8; ++i) t[u][i] = __ldcg(&ps[(c / 4 + i) * 128 + row]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                v[4 * i] += t[u][i].x; v[4 * i + 1] += t[u][i].y; v[4 * i + 2] += t[u][i].z; v[4 * i + 3] += t[u][i].w;
+              }
+          }
+          for (; s < p.splits; ++s) {
             const float4* ps = base + (long long)s * (BLOCK_N / 4) * 128;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -282,7 +339,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
             }
           }
           emit(c, v);
+          if (do_stats) col_stats(c, v);
         }
+        if (do_stats) flush_stats();
         if (et == 0) tickets[tile_lin] = 0;   // ready for the next launch
       }
     }

@@ -38,6 +38,8 @@ typedef struct {
   float* scratch;      /* split-K partial tiles (see ldnn_conv_query)                      */
   unsigned int* tickets; /* split-K arrival counters, zero-initialised once                */
   unsigned int a_lbo, a_sbo, b_lbo, b_sbo; /* debug: override smem-descriptor strides (0 = default) */
+  float* bn_sums;      /* fprop, optional: fp32 [2][Cout]; the epilogue ADDS per-channel sum and sum of
+                          squares of the output (fused BN statistics); caller zeroes it per step        */
 } ldnn_conv_desc;
 
 int ldnn_conv_query(const ldnn_conv_desc* d, size_t* scratch_bytes, size_t* ticket_count, int* launches);
@@ -89,6 +91,21 @@ int ldnn_bn_bwd_reduce(const void* dout, const void* out, const void* y, const f
 int ldnn_bn_bwd_apply(const void* dout, const void* out, const void* y, const float* save_mean,
                       const float* save_invstd, const float* gamma, const float* dgamma, const float* dbeta,
                       void* dy_raw, void* dres, int M, int C, int relu, int res_accumulate, void* stream);
+/* Fast path ("sums"): the conv epilogue accumulates per-channel sum / sum-of-squares into
+ * ldnn_conv_desc.bn_sums, so BN forward is one launch (scale/shift derived per CTA; CTA 0 updates the
+ * running statistics) and BN backward is reduce (red.add into sums[2][C]) + apply.  Summation order of
+ * the fp32 atomics is not fixed; use the ticketed entry points above for bit-reproducible statistics.
+ * training=0 normalises with the running statistics (sums ignored). */
+int ldnn_bn_fwd_apply_sums(const void* y, const float* sums /* [2][C] */, const float* gamma, const float* beta,
+                           float* running_mean, float* running_var, long long* num_batches_tracked,
+                           float* save_mean, float* save_invstd, const void* residual, void* out, int M, int C,
+                           int relu, int training, float eps, float momentum, void* stream);
+int ldnn_bn_bwd_reduce_sums(const void* dout, const void* out, const void* y, const float* save_mean,
+                            const float* save_invstd, float* sums /* [2][C], zeroed by the caller */, int M, int C,
+                            int chunks, int relu, void* stream);
+int ldnn_bn_bwd_apply_sums(const void* dout, const void* out, const void* y, const float* save_mean,
+                           const float* save_invstd, const float* gamma, const float* sums, void* dy_raw, void* dres,
+                           float* dgamma, float* dbeta, int M, int C, int relu, int res_accumulate, void* stream);
 /* 3x3/s2/p1-style max pool on NHWC bf16 (+ backward), ResNet-50 stem */
 int ldnn_maxpool_fwd(const void* x, void* y, int N, int H, int W, int C, int k, int stride, int pad, void* stream);
 int ldnn_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, int k,

@@ -19,6 +19,7 @@ The flat parameter layout is *internal* (KRSC, stem rows zero-padded to a multip
 from __future__ import annotations
 
 import math
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -57,7 +58,10 @@ class NativeEngine(Engine):
         if not L.available():
             raise L.LdnnError("libldnn_b200.so is not built; run `python -m ldnn_b200.build`")
         self.spec, self.device, self.max_batch = spec, canonical_device(device), batch_size
-        self.use_graph = use_graph
+        self.use_graph = use_graph and not os.environ.get("LDNN_NO_GRAPH")
+        # BN statistics: fused into the conv epilogue with fp32 red.add (fast, summation order not
+        # fixed) or the ticketed two-level reduction (bit-reproducible, ~2x more launches).
+        self.deterministic = bool(os.environ.get("LDNN_DETERMINISTIC"))
         torch.cuda.set_device(self.device)
         # ---- geometry ------------------------------------------------------------
         self.info: Dict[str, _ConvInfo] = {}
@@ -92,6 +96,8 @@ class NativeEngine(Engine):
         self.running_mean, self.running_var = z(c_tot), torch.ones(c_tot, dtype=torch.float32, device=self.device)
         self.nbt = z(len(self.bn_off), torch.int64)
         self.save_mean, self.save_invstd, self.scale, self.shift = z(c_tot), z(c_tot), z(c_tot), z(c_tot)
+        self.bn_sums = z(4 * c_tot)       # [fwd: per BN [2][C]] [bwd: per BN [2][C]]; zeroed once per step
+        self.c_tot = c_tot
         self._plans: Dict[Tuple[int, bool], "_StepPlan"] = {}
         if init:
             ref = SpecNet(spec)
@@ -249,8 +255,9 @@ class _StepPlan:
         self._warm = False
 
     # -- helpers -----------------------------------------------------------------
-    def _chunks(self, M: int) -> int:
-        return max(1, min(296, M // 32))
+    def _chunks(self, M: int, C: int = 64) -> int:
+        """Row chunks of the BN reductions: (C/64 channel slabs) x chunks CTAs, ~2 waves at most."""
+        return max(1, min(M // 128, max(1, 296 // max(1, C // 64))))
 
     def _add(self, fn, launches: int = 1):
         self.ops.append(fn)
@@ -279,11 +286,13 @@ class _StepPlan:
         partial_max = 0
         for u in spec.conv_units():
             ci = eng.info[u.conv_key]
-            partial_max = max(partial_max, self._chunks(n * ci.P * ci.Q) * 2 * u.cout)
+            partial_max = max(partial_max, self._chunks(n * ci.P * ci.Q, u.cout) * 2 * u.cout)
         self.partial = torch.zeros(partial_max, dtype=torch.float32, device=dev)
         self.bn_ticket = torch.zeros(4, dtype=torch.int32, device=dev)
 
         # ---- forward ----
+        if self.training and not eng.deterministic:
+            self._add(lambda: eng.bn_sums.zero_())
         for u in spec.units:
             if isinstance(u, ConvBN):
                 self._fwd_unit(u, W, P)
@@ -325,26 +334,34 @@ class _StepPlan:
             col = self.col[u.conv_key]
             H0, W0, C0 = eng.slot_shape["x"]
             self._add(lambda: K.im2col_stem(self.x_in, col, n, C0, H0, W0, u.k, u.stride, u.pad, ci.kdim))
-            plan = K.ConvPlan(K.FPROP, n, ci.P, ci.Q, ci.kdim, u.cout, 1, 1, 0, col, w, yraw, workspace=self.ws)
-        else:
-            plan = K.ConvPlan(K.FPROP, n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad, self.act[u.src], w, yraw,
-                              workspace=self.ws)
-        self._add(plan.run, plan.num_launches)
         M, Cc = n * ci.P * ci.Q, u.cout
         o = eng.bn_off[u.bn_key]
         gamma, beta = P(u.bn_key + ".weight"), P(u.bn_key + ".bias")
         sc, sh = eng.scale[o:o + Cc], eng.shift[o:o + Cc]
         rm, rv = eng.running_mean[o:o + Cc], eng.running_var[o:o + Cc]
+        sm, si = eng.save_mean[o:o + Cc], eng.save_invstd[o:o + Cc]
+        nbt = eng.nbt[list(eng.bn_off).index(u.bn_key):][:1]
+        res = self.act[u.residual] if u.residual is not None else None
+        out = self.act[u.dst]
+        fast = not eng.deterministic
+        fsum = eng.bn_sums[2 * o:2 * o + 2 * Cc] if (fast and self.training) else None
+        if ci.im2col:
+            plan = K.ConvPlan(K.FPROP, n, ci.P, ci.Q, ci.kdim, u.cout, 1, 1, 0, self.col[u.conv_key], w, yraw,
+                              workspace=self.ws, bn_sums=fsum)
+        else:
+            plan = K.ConvPlan(K.FPROP, n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad, self.act[u.src], w, yraw,
+                              workspace=self.ws, bn_sums=fsum)
+        self._add(plan.run, plan.num_launches)
+        if fast:
+            self._add(lambda: K.bn_fwd_apply_sums(yraw, fsum, gamma, beta, rm, rv, nbt, sm, si, res, out, M, Cc, u.relu,
+                                                  self.training, BN_EPS, BN_MOMENTUM))
+            return
         if self.training:
-            sm, si = eng.save_mean[o:o + Cc], eng.save_invstd[o:o + Cc]
-            nbt = eng.nbt[list(eng.bn_off).index(u.bn_key):][:1]
-            chunks = self._chunks(M)
+            chunks = self._chunks(M, Cc)
             self._add(lambda: K.bn_fwd_stats(yraw, M, Cc, chunks, self.partial, self.bn_ticket, gamma, beta, rm, rv,
                                              nbt, sm, si, sc, sh, BN_EPS, BN_MOMENTUM))
         else:
             self._add(lambda: K.bn_eval_coeffs(gamma, beta, rm, rv, sc, sh, Cc, BN_EPS))
-        res = self.act[u.residual] if u.residual is not None else None
-        out = self.act[u.dst]
         self._add(lambda: K.bn_fwd_apply(yraw, sc, sh, res, out, M, Cc, u.relu))
 
     def _bwd_unit(self, u: ConvBN, W, P, G, written):
@@ -357,17 +374,23 @@ class _StepPlan:
         sm, si = eng.save_mean[o:o + Cc], eng.save_invstd[o:o + Cc]
         gamma = P(u.bn_key + ".weight")
         dgamma, dbeta = G(u.bn_key + ".weight"), G(u.bn_key + ".bias")
-        chunks = self._chunks(M)
-        self._add(lambda: K.bn_bwd_reduce(dout, out, yraw, sm, si, self.partial, self.bn_ticket[1:], M, Cc, chunks,
-                                          u.relu, dgamma, dbeta))
+        chunks = self._chunks(M, Cc)
         dyr = self.dy_raw[:M * Cc]
         dres, res_acc = None, False
         if u.residual is not None:
             dres = self.dact[u.residual]
             res_acc = u.residual in written
             written.add(u.residual)
-        self._add(lambda: K.bn_bwd_apply(dout, out, yraw, sm, si, gamma, dgamma, dbeta, dyr, dres, M, Cc, u.relu,
-                                         res_acc))
+        if eng.deterministic:
+            self._add(lambda: K.bn_bwd_reduce(dout, out, yraw, sm, si, self.partial, self.bn_ticket[1:], M, Cc,
+                                              chunks, u.relu, dgamma, dbeta))
+            self._add(lambda: K.bn_bwd_apply(dout, out, yraw, sm, si, gamma, dgamma, dbeta, dyr, dres, M, Cc, u.relu,
+                                             res_acc))
+        else:
+            bsum = eng.bn_sums[2 * eng.c_tot + 2 * o:2 * eng.c_tot + 2 * o + 2 * Cc]
+            self._add(lambda: K.bn_bwd_reduce_sums(dout, out, yraw, sm, si, bsum, M, Cc, chunks, u.relu))
+            self._add(lambda: K.bn_bwd_apply_sums(dout, out, yraw, sm, si, gamma, bsum, dyr, dres, dgamma, dbeta, M,
+                                                  Cc, u.relu, res_acc))
         w = W(u.conv_key + ".weight")
         gw = G(u.conv_key + ".weight")
         if ci.im2col:

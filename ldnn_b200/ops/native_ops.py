@@ -23,19 +23,20 @@ class ConvPlan:
     def __init__(self, mode: int, N: int, H: int, W: int, Cin: int, Cout: int, R: int, stride: int, pad: int,
                  x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, dw: Optional[torch.Tensor] = None,
                  addend: Optional[torch.Tensor] = None, accumulate: bool = False, block_n: int = 0, splits: int = 0,
-                 workspace=None, desc_override=None):
+                 workspace=None, desc_override=None, bn_sums: Optional[torch.Tensor] = None):
         d = L.ConvDesc()
         d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
         d.block_n, d.splits, d.accumulate = block_n, splits, int(accumulate)
         d.x, d.w, d.y = x.data_ptr(), (0 if w is None else w.data_ptr()), y.data_ptr()
         d.dw = 0 if dw is None else dw.data_ptr()
         d.addend = 0 if addend is None else addend.data_ptr()
+        d.bn_sums = 0 if bn_sums is None else bn_sums.data_ptr()
         if desc_override:
             d.a_lbo, d.a_sbo, d.b_lbo, d.b_sbo = desc_override
         sb, tk, nl = C.c_size_t(0), C.c_size_t(0), C.c_int(0)
         L.check(L.lib().ldnn_conv_query(C.byref(d), C.byref(sb), C.byref(tk), C.byref(nl)))
         self.scratch_bytes, self.ticket_count, self.num_launches = sb.value, tk.value, nl.value
-        self._keep = [x, w, y, dw, addend]
+        self._keep = [x, w, y, dw, addend, bn_sums]
         if sb.value:
             if workspace is not None:
                 scratch, tickets = workspace.take(sb.value, tk.value)
@@ -125,6 +126,26 @@ def bn_bwd_apply(dout, out, y, save_mean, save_invstd, gamma, dgamma, dbeta, dy_
     L.check(L.lib().ldnn_bn_bwd_apply(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
                                       L.ptr(gamma), L.ptr(dgamma), L.ptr(dbeta), L.ptr(dy_raw), L.ptr(dres), M, Cc,
                                       int(relu), int(res_accumulate), L.stream_ptr()))
+
+
+def bn_fwd_apply_sums(y, sums, gamma, beta, rmean, rvar, nbt, save_mean, save_invstd, residual, out, M, Cc, relu,
+                      training, eps=1e-5, momentum=0.1):
+    L.check(L.lib().ldnn_bn_fwd_apply_sums(L.ptr(y), L.ptr(sums), L.ptr(gamma), L.ptr(beta), L.ptr(rmean), L.ptr(rvar),
+                                           L.ptr(nbt), L.ptr(save_mean), L.ptr(save_invstd), L.ptr(residual),
+                                           L.ptr(out), M, Cc, int(relu), int(training), C.c_float(eps),
+                                           C.c_float(momentum), L.stream_ptr()))
+
+
+def bn_bwd_reduce_sums(dout, out, y, save_mean, save_invstd, sums, M, Cc, chunks, relu):
+    L.check(L.lib().ldnn_bn_bwd_reduce_sums(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
+                                            L.ptr(sums), M, Cc, chunks, int(relu), L.stream_ptr()))
+
+
+def bn_bwd_apply_sums(dout, out, y, save_mean, save_invstd, gamma, sums, dy_raw, dres, dgamma, dbeta, M, Cc, relu,
+                      res_accumulate):
+    L.check(L.lib().ldnn_bn_bwd_apply_sums(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
+                                           L.ptr(gamma), L.ptr(sums), L.ptr(dy_raw), L.ptr(dres), L.ptr(dgamma),
+                                           L.ptr(dbeta), M, Cc, int(relu), int(res_accumulate), L.stream_ptr()))
 
 
 def maxpool_fwd(x, y, N, H, W, Cc, k, stride, pad):

@@ -117,7 +117,8 @@ class FusedExchanger:
         for i in range(L.MAX_RANKS):
             e.grads[i], e.params[i] = tab[i], ptab[i]
         f = self.engine.flat
-        e.m, e.v = f.m.data_ptr(), (f.v.data_ptr() if f.v is not None else 0)
+        e.m = f.m.data_ptr() if f.m is not None else 0
+        e.v = f.v.data_ptr() if f.v is not None else 0
         sh = getattr(self.engine, "shadow", None)
         e.shadow = 0 if sh is None else sh.data_ptr()
         e.n = self.n

@@ -1,0 +1,88 @@
+"""Worker for the multi-GPU tests (one process per GPU, launched by torchrun): FusedExchanger over real
+CUDA-IPC peer mappings vs the fp64 mixing-matrix oracle, for every topology / aggregation / target."""
+import itertools
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    import torch.distributed as dist
+    from ldnn_b200.config import Config, resolve
+    from ldnn_b200.engine import OptimConfig, TorchEngine
+    from ldnn_b200.launch import init_runtime, shutdown
+    from ldnn_b200.parallel.exchange import ExchangeSpec, mixing_matrix
+    from ldnn_b200.parallel.fused import FusedExchanger
+    from test_flat_optimizer import tiny_spec
+
+    rt = init_runtime("nccl", seed=0)
+    ws, r, dev = rt.world_size, rt.rank, rt.device
+    eng = TorchEngine(tiny_spec(), dev, OptimConfig(kind="adam", lr=1e-2))
+    n = eng.flat.total
+    sw = [float(i + 1) for i in range(ws)]
+
+    def all_data(seed):
+        g = torch.Generator().manual_seed(seed)
+        return torch.randn(ws, n, generator=g, dtype=torch.float64)
+
+    checked = 0
+    combos = [("allreduce", "allreduce"), ("ring", "allreduce"), ("double_ring", "allreduce"), ("ring", "gossip"),
+              ("double_ring", "gossip")]
+    for (topo, sem), agg, target in itertools.product(combos, ["equal", "shard", "weighted"], ["grads", "params"]):
+        sp = ExchangeSpec(topo, sem, agg, 0.7, sw, ws)
+        ex = FusedExchanger(sp, rt, eng, comm_blocks=8, watchdog_ms=5000)
+        for rep in range(2):
+            X = all_data(100 * checked + rep)
+            buf = eng.flat.grads if target == "grads" else eng.flat.params
+            buf.copy_(X[r].float())
+            if target == "grads":
+                ex.exchange_grads(eng, apply_update=False)
+            else:
+                ex.exchange_weights(eng)
+            ex.check()
+            want = (torch.from_numpy(mixing_matrix(sp)) @ X)[r].to(dev)
+            err = float((buf.double() - want).abs().max())
+            assert err < 1e-5, (topo, sem, agg, target, rep, err)
+        ex.close()
+        checked += 1
+
+    # fused update tail: identical parameters everywhere, equal to the local oracle
+    for topo in ["allreduce", "ring", "double_ring"]:
+        sp = ExchangeSpec(topo, "allreduce", "equal", 0.5, None, ws)
+        ex = FusedExchanger(sp, rt, eng, comm_blocks=8, watchdog_ms=5000)
+        ref = TorchEngine(tiny_spec(), dev, OptimConfig(kind="adam", lr=1e-2))
+        eng.flat.params.copy_(all_data(5)[0].float())          # same starting point on every rank
+        ref.flat.params.copy_(eng.flat.params)
+        eng.flat.m.zero_(); eng.flat.v.zero_(); eng.flat.step = 0
+        for step in range(3):
+            X = all_data(7000 + step)
+            eng.flat.grads.copy_(X[r].float())
+            ex.exchange_grads(eng, apply_update=True)
+            ex.check()
+            ref.flat.optimizer_step(X.mean(0).float().to(dev))
+        diff = (eng.flat.params - ref.flat.params).abs()
+        assert float((diff > 1e-5).float().mean()) < 1e-3 and float(diff.max()) < 3e-2, (topo, float(diff.max()))
+        gathered = [torch.empty_like(eng.flat.params) for _ in range(ws)]
+        dist.all_gather(gathered, eng.flat.params)
+        assert all(torch.equal(g, gathered[0]) for g in gathered), topo
+        ex.close()
+
+    # broadcast
+    sp = ExchangeSpec("allreduce", "allreduce", "equal", 0.5, None, ws)
+    ex = FusedExchanger(sp, rt, eng, comm_blocks=8, watchdog_ms=5000)
+    eng.flat.params.fill_(float(r + 1))
+    ex.broadcast_state(eng, src=0)
+    assert float(eng.flat.params.min()) == 1.0 == float(eng.flat.params.max())
+    ex.close()
+    if r == 0:
+        print(f"MGPU_OK world={ws} combos={checked}")
+    shutdown(rt)
+
+
+if __name__ == "__main__":
+    main()

@@ -9,7 +9,7 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("M,C", [(64 * 32 * 32, 64), (64 * 16 * 16, 128), (64 * 2 * 2, 1024), (6 * 8 * 8, 256),
-                                 (37, 2048), (100, 192)])
+                                 (37, 2048), (100, 192), (64 * 4 * 4, 512)])
 @pytest.mark.parametrize("relu,use_res", [(True, True), (True, False), (False, False)])
 def test_bn_forward_backward(M, C, relu, use_res):
     from ldnn_b200.ops import native_ops as K
@@ -52,7 +52,8 @@ def test_bn_forward_backward(M, C, relu, use_res):
     K.bn_bwd_apply(dout, out, y, sm, si, gamma, dgamma, dbeta, dyr, dres, M, C, relu, False)
     o.backward(dout.float())
     scale = float(yr.grad.abs().max()) + 1e-6
-    assert float((dyr.float() - yr.grad).abs().max()) / scale < 3e-2
+    bad = ((dyr.float() - yr.grad).abs() / scale > 3e-2).float().mean()      # ReLU-mask flips at ~0, see below
+    assert float(bad) < 2e-3, float(bad)
     assert torch.allclose(dgamma, gr.grad, rtol=2e-2, atol=2e-2 * float(gr.grad.abs().max()))
     assert torch.allclose(dbeta, br.grad, rtol=2e-2, atol=2e-2 * float(br.grad.abs().max()))
     if use_res:
@@ -128,3 +129,62 @@ def test_im2col_stem_matches_unfold():
     K.im2col_stem(x, col, N, C, H, W, R, 1, 1, 64)
     ref = F.unfold(x, R, padding=1).view(N, C, R * R, H * W).permute(0, 3, 2, 1).reshape(N * H * W, R * R * C)
     assert torch.equal(col[:, :27], ref.bfloat16()) and float(col[:, 27:].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (64, 2, 2, 1024, 1024, 3, 1, 1), (6, 8, 8, 256, 512, 3, 2, 1),
+                                  (3, 14, 14, 256, 256, 3, 1, 1)])
+@pytest.mark.parametrize("use_res", [False, True])
+def test_conv_fused_stats_and_sums_bn(case, use_res):
+    """conv epilogue accumulates sum / sum-of-squares; BN fwd/bwd 'sums' kernels vs fp32 torch."""
+    from gpu_util import fp32_mode, make_conv_case, ref_conv
+    from ldnn_b200.ops import native_ops as K
+    fp32_mode()
+    N, H, W, Cin, Cout, R, s, p = case
+    x, w, dy, P, Q = make_conv_case(*case)
+    M, C = N * P * Q, Cout
+    y = torch.empty(N, P, Q, Cout, device="cuda", dtype=torch.bfloat16)
+    sums = torch.zeros(2 * C, device="cuda")
+    plan = K.ConvPlan(K.FPROP, N, H, W, Cin, Cout, R, s, p, x, w.view(Cout, -1), y, bn_sums=sums)
+    plan.run()
+    torch.cuda.synchronize()
+    yr = ref_conv(x, w, s, p).view(M, C)
+    assert torch.allclose(sums[:C], yr.sum(0), rtol=2e-3, atol=2e-3 * float(yr.abs().sum(0).max()))
+    assert torch.allclose(sums[C:], (yr * yr).sum(0), rtol=5e-3)
+    g = torch.Generator().manual_seed(5)
+    gamma, beta = (torch.rand(C, generator=g) + 0.5).cuda(), torch.randn(C, generator=g).cuda()
+    res = torch.randn(M, C, generator=g).cuda().bfloat16() if use_res else None
+    dout = torch.randn(M, C, generator=g).cuda().bfloat16()
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    nbt = torch.zeros(1, dtype=torch.int64, device="cuda")
+    sm, si = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    out = torch.empty(M, C, device="cuda", dtype=torch.bfloat16)
+    K.bn_fwd_apply_sums(y, sums, gamma, beta, rm, rv, nbt, sm, si, res, out, M, C, True, True)
+    yy = y.view(M, C).float().requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rrm, rrv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    o = F.batch_norm(yy, rrm, rrv, gr, br, True, 0.1, 1e-5)
+    rr = res.float().requires_grad_(True) if use_res else None
+    o = F.relu(o + rr) if use_res else F.relu(o)
+    assert torch.allclose(out.float(), o, atol=4e-2, rtol=2e-2)
+    assert torch.allclose(rm, rrm, atol=2e-3) and torch.allclose(rv, rrv, atol=2e-3, rtol=2e-3) and int(nbt) == 1
+    bsum = torch.zeros(2 * C, device="cuda")
+    dgamma, dbeta = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    dyr = torch.empty(M, C, device="cuda", dtype=torch.bfloat16)
+    dres = torch.empty(M, C, device="cuda", dtype=torch.bfloat16) if use_res else None
+    chunks = max(1, min(M // 128, max(1, 296 // max(1, C // 64))))
+    K.bn_bwd_reduce_sums(dout, out, y, sm, si, bsum, M, C, chunks, True)
+    K.bn_bwd_apply_sums(dout, out, y, sm, si, gamma, bsum, dyr, dres, dgamma, dbeta, M, C, True, False)
+    o.backward(dout.float())
+    scale = float(yy.grad.abs().max()) + 1e-6
+    # pre-activations within rounding distance of 0 may flip the ReLU mask between the bf16 kernel and
+    # the fp32 oracle; allow a vanishing fraction of such elements
+    bad = ((dyr.float() - yy.grad).abs() / scale > 4e-2).float().mean()
+    assert float(bad) < 2e-3, float(bad)
+    assert torch.allclose(dgamma, gr.grad, rtol=3e-2, atol=3e-2 * float(gr.grad.abs().max()))
+    assert torch.allclose(dbeta, br.grad, rtol=3e-2, atol=3e-2 * float(br.grad.abs().max()))
+    if use_res:
+        assert torch.allclose(dres.float(), rr.grad, atol=2e-2, rtol=2e-2)
+    # eval mode ignores the sums
+    K.bn_fwd_apply_sums(y, None, gamma, beta, rm, rv, nbt, sm, si, None, out, M, C, False, False)
+    ref = F.batch_norm(y.view(M, C).float(), rm, rv, gamma, beta, False, 0.1, 1e-5)
+    assert torch.allclose(out.float(), ref, atol=4e-2, rtol=2e-2)
