@@ -68,8 +68,10 @@ struct Launch {
   ConvMaps maps;
   ConvParams p;
   dim3 grid;
-  size_t scratch_floats = 0;   // offset bookkeeping
-  size_t ticket_off = 0, scratch_off = 0, tickets = 0;
+  size_t scratch_floats = 0, tickets = 0;   // split-K workspace this launch needs
+  size_t ticket_off = 0, scratch_off = 0;
+  bool uses_split_scratch = false;
+  int covered_classes = 1;                  // dgrad: parity classes that have taps
 };
 struct Plan {
   int mode, block_n;
@@ -81,13 +83,13 @@ struct Plan {
   float* stats;
 };
 
-static void pixel_box(int Wd, int Hd, int Nd, int target, ConvParams& p) {
+static void pixel_box(int Wd, int Hd, int Nd, int target, ConvParams& p, ConvClass& c) {
   p.bw = std::min(next_pow2(Wd), target);
   p.bh = std::min(next_pow2(Hd), target / p.bw);
   p.bn = target / (p.bw * p.bh);
-  p.tiles_w = cdiv(Wd, p.bw);
-  p.tiles_h = cdiv(Hd, p.bh);
-  p.Wd = Wd; p.Hd = Hd; p.Nd = Nd;
+  c.tiles_w = cdiv(Wd, p.bw);
+  c.tiles_h = cdiv(Hd, p.bh);
+  c.Wd = Wd; c.Hd = Hd; p.Nd = Nd;
 }
 
 static int pick_splits(int tiles, int iters, int requested) {
@@ -108,13 +110,23 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   LDNN_ARG(d.mode >= 0 && d.mode <= 2, "bad conv mode %d", d.mode);
   LDNN_ARG(d.Cin % 64 == 0 && d.Cout % 64 == 0, "Cin=%d / Cout=%d must be multiples of 64", d.Cin, d.Cout);
   LDNN_ARG(d.stride == 1 || d.stride == 2, "stride %d unsupported", d.stride);
-  LDNN_ARG(d.R * d.R <= 16, "filter %dx%d too large for the tap table", d.R, d.R);
+  LDNN_ARG(d.R * d.R <= 12, "filter %dx%d too large for the tap table", d.R, d.R);
   const int T = d.R * d.R;
   const int P = (d.H + 2 * d.pad - d.R) / d.stride + 1, Q = (d.W + 2 * d.pad - d.R) / d.stride + 1;
   const int n_total = (d.mode == MODE_FPROP) ? d.Cout : d.Cin;
+  // pixel tiles of the output-side grid (for the tile-count heuristics)
+  const int grid_w = (d.mode == MODE_DGRAD) ? d.W : Q, grid_h = (d.mode == MODE_DGRAD) ? d.H : P;
   int bn_ = d.block_n;
-  if (bn_ == 0) bn_ = (n_total % 128 == 0) ? 128 : 64;
-  if (d.mode == MODE_WGRAD && d.block_n == 0) bn_ = (n_total % 256 == 0) ? 256 : ((n_total % 128 == 0) ? 128 : 64);
+  if (bn_ == 0) {
+    if (d.mode == MODE_WGRAD) {
+      bn_ = (n_total % 256 == 0) ? 256 : ((n_total % 128 == 0) ? 128 : 64);
+    } else {
+      bn_ = (n_total % 128 == 0) ? 128 : 64;
+      // few output tiles: prefer narrower tiles (more CTAs, fewer K splits to fold) over split-K
+      const long long m_tiles_est = cdiv((long long)d.N * grid_h * grid_w, 128);
+      if (bn_ == 128 && m_tiles_est * (n_total / 128) < 64) bn_ = 64;
+    }
+  }
   LDNN_ARG(bn_ == 64 || bn_ == 128 || bn_ == 256, "block_n %d", bn_);
   LDNN_ARG(n_total % bn_ == 0, "N=%d not a multiple of block_n=%d", n_total, bn_);
   plan.mode = d.mode; plan.block_n = bn_;
@@ -125,7 +137,6 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
 
   const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(d.x);
   const __nv_bfloat16* yb = reinterpret_cast<const __nv_bfloat16*>(d.y);
-  size_t scratch_off = 0, ticket_off = 0;
 
   // parity views of x for strided convs: view (hp,wp) has rows h = 2a+hp
   auto x_view_map = [&](CUtensorMap* m, int hp, int wp, const uint32_t* box) -> int {
@@ -146,12 +157,12 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
     return make_map(m, d.w, 2, dims, str, box);
   };
   // forward-style tap table: input row = stride*p - pad + r
-  auto fwd_taps = [&](ConvParams& p) {
-    p.num_taps = T;
+  auto fwd_taps = [&](ConvClass& c) {
+    c.num_taps = T;
     for (int r = 0; r < d.R; ++r)
       for (int s = 0; s < d.R; ++s) {
         const int th = r - d.pad, tw = s - d.pad;
-        TapEntry& te = p.taps[r * d.R + s];
+        TapEntry& te = c.taps[r * d.R + s];
         te.map = (int8_t)(posmod(th, d.stride) * 2 + posmod(tw, d.stride));
         if (d.stride == 1) te.map = 0;
         te.dh = (int8_t)floordiv(th, d.stride);
@@ -159,40 +170,33 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
         te.wtap = (int8_t)(r * d.R + s);
       }
   };
-  auto defaults = [&](ConvParams& p) {
-    memset(&p, 0, sizeof(p));
-    p.accumulate = d.accumulate;
-    p.n_total = n_total;
-    // K-major SW128 tile: 8-row groups 1024 B apart; MN-major: 64-wide MN blocks 8192 B apart,
-    // 8-row K groups 1024 B apart.
-    p.a_lbo = d.a_lbo ? d.a_lbo : (d.mode == MODE_WGRAD ? 8192u : 16u);
-    p.a_sbo = d.a_sbo ? d.a_sbo : 1024u;
-    p.b_lbo = d.b_lbo ? d.b_lbo : (d.mode == MODE_FPROP ? 16u : 8192u);
-    p.b_sbo = d.b_sbo ? d.b_sbo : 1024u;
-  };
-  auto finish = [&](Launch& L, int tiles_for_split) {
-    ConvParams& p = L.p;
-    p.splits = pick_splits(tiles_for_split, p.iters_total, d.splits);
-    p.iters_per_split = cdiv(p.iters_total, p.splits);
-    if (p.splits > 1) {
-      L.scratch_off = scratch_off; L.ticket_off = ticket_off;
-      scratch_off += (size_t)tiles_for_split * p.splits * 128 * bn_;
-      ticket_off += tiles_for_split;
-    }
-  };
+  Launch L;
+  ConvParams& p = L.p;
+  memset(&p, 0, sizeof(p));
+  p.accumulate = d.accumulate;
+  p.n_total = n_total;
+  p.num_classes = 1;
+  // K-major SW128 tile: 8-row groups 1024 B apart; MN-major: 64-wide MN blocks 8192 B apart,
+  // 8-row K groups 1024 B apart.
+  p.a_lbo = d.a_lbo ? d.a_lbo : (d.mode == MODE_WGRAD ? 8192u : 16u);
+  p.a_sbo = d.a_sbo ? d.a_sbo : 1024u;
+  p.b_lbo = d.b_lbo ? d.b_lbo : (d.mode == MODE_FPROP ? 16u : 8192u);
+  p.b_sbo = d.b_sbo ? d.b_sbo : 1024u;
+  size_t scratch_floats = 0, tickets = 0;
 
   if (d.mode == MODE_FPROP) {
-    Launch L;
-    ConvParams& p = L.p;
-    defaults(p);
-    pixel_box(Q, P, d.N, 128, p);
-    fwd_taps(p);
+    ConvClass& c = p.cls[0];
+    pixel_box(Q, P, d.N, 128, p, c);
+    fwd_taps(c);
     p.kb_per_tap = d.Cin / 64; p.red_ch = d.Cin;
-    p.iters_total = T * p.kb_per_tap;
-    p.out_base = 0; p.sW = d.Cout; p.sH = (long long)Q * d.Cout; p.sN = (long long)P * Q * d.Cout;
-    const int m_tiles = p.tiles_w * p.tiles_h * cdiv(d.N, p.bn), n_tiles = d.Cout / bn_;
-    finish(L, m_tiles * n_tiles);
-    L.grid = dim3(m_tiles, n_tiles, p.splits);
+    c.iters_total = T * p.kb_per_tap;
+    c.out_base = 0; p.sW = d.Cout; p.sH = (long long)Q * d.Cout; p.sN = (long long)P * Q * d.Cout;
+    const int m_tiles = c.tiles_w * c.tiles_h * cdiv(d.N, p.bn), n_tiles = d.Cout / bn_;
+    c.splits = pick_splits(m_tiles * n_tiles, c.iters_total, d.splits);
+    c.iters_per_split = cdiv(c.iters_total, c.splits);
+    p.max_splits = c.splits;
+    if (c.splits > 1) { scratch_floats = (size_t)m_tiles * n_tiles * c.splits * 128 * bn_; tickets = (size_t)m_tiles * n_tiles; }
+    L.grid = dim3(m_tiles, n_tiles, c.splits);
     if (!dry) {
       uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
       const int nviews = d.stride == 1 ? 1 : 4;
@@ -203,22 +207,27 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
       int rc = w_map(&L.maps.other, bn_);
       if (rc) return rc;
     }
-    plan.launches.push_back(L);
   } else if (d.mode == MODE_DGRAD) {
-    // one launch per output parity class (1 class for stride 1)
+    // one class per output parity (1 class for stride 1), all in one launch
+    p.kb_per_tap = d.Cout / 64; p.red_ch = d.Cout;
+    p.sW = (long long)d.stride * d.Cin; p.sH = (long long)d.stride * d.W * d.Cin; p.sN = (long long)d.H * d.W * d.Cin;
+    const int n_tiles = d.Cin / bn_;
+    int ncls = 0, m_total = 0, covered = 0;
+    // all classes share one pixel box: size it from the largest class (parity 0,0)
+    ConvClass tmp;
+    pixel_box(cdiv(d.W, d.stride), cdiv(d.H, d.stride), d.N, 128, p, tmp);
     for (int hp = 0; hp < d.stride; ++hp)
       for (int wp = 0; wp < d.stride; ++wp) {
-        Launch L;
-        ConvParams& p = L.p;
-        defaults(p);
+        ConvClass c;
+        memset(&c, 0, sizeof(c));
         const int Hs = cdiv(d.H - hp, d.stride), Ws = cdiv(d.W - wp, d.stride);
-        pixel_box(Ws, Hs, d.N, 128, p);
+        c.Wd = Ws; c.Hd = Hs; c.tiles_w = cdiv(Ws, p.bw); c.tiles_h = cdiv(Hs, p.bh);
         int nt = 0;
         for (int r = 0; r < d.R; ++r)
           for (int s = 0; s < d.R; ++s) {
             const int th = hp + d.pad - r, tw = wp + d.pad - s;
             if (posmod(th, d.stride) || posmod(tw, d.stride)) continue;
-            TapEntry& te = p.taps[nt++];
+            TapEntry& te = c.taps[nt++];
             te.map = 0; te.dh = (int8_t)floordiv(th, d.stride); te.dw = (int8_t)floordiv(tw, d.stride);
             te.wtap = (int8_t)(r * d.R + s);
           }
@@ -226,35 +235,50 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
           LDNN_ARG(d.accumulate, "dgrad parity class (%d,%d) has no taps and accumulate=0", hp, wp);
           continue;
         }
-        p.num_taps = nt;
-        p.kb_per_tap = d.Cout / 64; p.red_ch = d.Cout;
-        p.iters_total = nt * p.kb_per_tap;
-        p.out_base = ((long long)hp * d.W + wp) * d.Cin;
-        p.sW = (long long)d.stride * d.Cin; p.sH = (long long)d.stride * d.W * d.Cin; p.sN = (long long)d.H * d.W * d.Cin;
-        const int m_tiles = p.tiles_w * p.tiles_h * cdiv(d.N, p.bn), n_tiles = d.Cin / bn_;
-        finish(L, m_tiles * n_tiles);
-        L.grid = dim3(m_tiles, n_tiles, p.splits);
-        if (!dry) {
-          uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
-          for (int v = 0; v < 4; ++v) { int rc = y_map(&L.maps.act[v], box); if (rc) return rc; }
-          int rc = w_map(&L.maps.other, 64);
-          if (rc) return rc;
-        }
-        plan.launches.push_back(L);
+        ++covered;
+        c.num_taps = nt;
+        c.iters_total = nt * p.kb_per_tap;
+        c.out_base = ((long long)hp * d.W + wp) * d.Cin;
+        c.m_begin = m_total;
+        m_total += c.tiles_w * c.tiles_h * cdiv(d.N, p.bn);
+        p.cls[ncls++] = c;
       }
+    LDNN_ARG(ncls >= 1, "dgrad: no taps at all");
+    p.num_classes = ncls;
+    L.covered_classes = covered;
+    p.max_splits = 1;
+    for (int i = 0; i < ncls; ++i) {
+      ConvClass& c = p.cls[i];
+      c.splits = pick_splits(m_total * n_tiles, c.iters_total, d.splits);
+      c.iters_per_split = cdiv(c.iters_total, c.splits);
+      p.max_splits = std::max(p.max_splits, c.splits);
+    }
+    if (p.max_splits > 1) { scratch_floats = (size_t)m_total * n_tiles * p.max_splits * 128 * bn_; tickets = (size_t)m_total * n_tiles; }
+    L.grid = dim3(m_total, n_tiles, p.max_splits);
+    if (!dry) {
+      uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+      for (int v = 0; v < 4; ++v) { int rc = y_map(&L.maps.act[v], box); if (rc) return rc; }
+      int rc = w_map(&L.maps.other, 64);
+      if (rc) return rc;
+    }
   } else {
     LDNN_ARG(d.Cout % 128 == 0 || d.Cout == 64, "wgrad needs Cout %% 128 == 0 (or 64)");
-    Launch L;
-    ConvParams& p = L.p;
-    defaults(p);
-    pixel_box(Q, P, d.N, 64, p);
-    fwd_taps(p);
-    p.iters_total = p.tiles_w * p.tiles_h * cdiv(d.N, p.bn);
+    ConvClass& c = p.cls[0];
+    pixel_box(Q, P, d.N, 64, p, c);
+    fwd_taps(c);
+    c.iters_total = c.tiles_w * c.tiles_h * cdiv(d.N, p.bn);
     p.sN = (long long)T * d.Cin;     // row stride of dw
     p.red_ch = d.Cout;               // rows that exist (store mask)
+    p.atomic_out = d.atomic_out;
     const int m_tiles = cdiv(d.Cout, 128), n_tiles = d.Cin / bn_;
-    finish(L, m_tiles * n_tiles * T);
-    L.grid = dim3(m_tiles, n_tiles, T * p.splits);
+    c.splits = pick_splits(m_tiles * n_tiles * T, c.iters_total, d.splits);
+    c.iters_per_split = cdiv(c.iters_total, c.splits);
+    p.max_splits = c.splits;
+    if (c.splits > 1 && !p.atomic_out) {
+      scratch_floats = (size_t)m_tiles * n_tiles * T * c.splits * 128 * bn_;
+      tickets = (size_t)m_tiles * n_tiles * T;
+    }
+    L.grid = dim3(m_tiles, n_tiles, T * c.splits);
     if (!dry) {
       uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
       const int nviews = d.stride == 1 ? 1 : 4;
@@ -265,11 +289,10 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
       int rc = y_map(&L.maps.other, box);
       if (rc) return rc;
     }
-    plan.launches.push_back(L);
   }
-  plan.launches.empty() ? (void)0 : (void)0;
-  // stash totals in the first launch for the query
-  if (!plan.launches.empty()) { plan.launches[0].scratch_floats = scratch_off; plan.launches[0].tickets = ticket_off; }
+  L.scratch_floats = scratch_floats; L.tickets = tickets;
+  L.uses_split_scratch = scratch_floats > 0;
+  plan.launches.push_back(L);
   return LDNN_OK;
 }
 
@@ -307,13 +330,15 @@ extern "C" const char* ldnn_last_error(void) { return g_err; }
 extern "C" int ldnn_version(void) { return 100; }
 extern "C" unsigned long long ldnn_launch_count(void) { return g_launches.load(); }
 
-extern "C" int ldnn_conv_query(const ldnn_conv_desc* d, size_t* scratch_bytes, size_t* ticket_count, int* launches) {
+extern "C" int ldnn_conv_query(const ldnn_conv_desc* d, size_t* scratch_bytes, size_t* ticket_count, int* launches,
+                               int* covered_classes) {
   Plan pl;
   int rc = build(*d, pl, true);
   if (rc) return rc;
   if (scratch_bytes) *scratch_bytes = pl.launches.empty() ? 0 : pl.launches[0].scratch_floats * sizeof(float);
   if (ticket_count) *ticket_count = pl.launches.empty() ? 0 : pl.launches[0].tickets;
   if (launches) *launches = (int)pl.launches.size();
+  if (covered_classes) *covered_classes = pl.launches.empty() ? 0 : pl.launches[0].covered_classes;
   return LDNN_OK;
 }
 
@@ -322,7 +347,7 @@ extern "C" int ldnn_conv_plan_create(const ldnn_conv_desc* d, void** plan) {
   int rc = build(*d, *pl, false);
   if (rc) { delete pl; return rc; }
   bool need_scratch = false;
-  for (auto& L : pl->launches) need_scratch |= L.p.splits > 1;
+  for (auto& L : pl->launches) need_scratch |= L.uses_split_scratch;
   if (need_scratch && (!d->scratch || !d->tickets)) {
     delete pl;
     set_last_error("conv plan uses split-K but scratch/tickets were not provided");

@@ -31,22 +31,34 @@ struct TapEntry {
   int8_t wtap;  // tap index inside the weight tensor (r*S+s)
 };
 
-struct ConvParams {
-  int bw, bh, bn;          // pixel box (w, h, n); bw*bh*bn = 128 (fprop/dgrad M tile) or 64 (wgrad K block)
-  int tiles_w, tiles_h;    // boxes along w and h of the pixel grid
+// One output "class".  fprop / wgrad have a single class; a stride-2 dgrad has one class per output
+// parity (h%2, w%2) — all of them run in ONE launch (CTAs find their class from blockIdx.x).
+struct ConvClass {
+  int m_begin;             // first blockIdx.x of this class
   int num_taps;
-  int kb_per_tap;          // fprop/dgrad: reduction channels / 64
+  int tiles_w, tiles_h;    // boxes along w and h of this class's pixel grid
+  int Wd, Hd;              // extents of the pixel grid (store masks)
   int iters_total;         // fprop/dgrad: num_taps*kb_per_tap; wgrad: number of pixel blocks
   int iters_per_split;
   int splits;
-  int Wd, Hd, Nd;          // extents of the pixel grid (for store masks)
-  int red_ch;              // fprop: Cin, dgrad: Cout (channels of the reduction dim) — weight column stride per tap
+  int pad_;
+  long long out_base;      // element offset of pixel (0,0,0) of this class
+  TapEntry taps[12];
+};
+
+struct ConvParams {
+  int bw, bh, bn;          // pixel box (w, h, n); bw*bh*bn = 128 (fprop/dgrad M tile) or 64 (wgrad K block)
+  int Nd;                  // batch (store mask)
+  int kb_per_tap;          // fprop/dgrad: reduction channels / 64
+  int red_ch;              // fprop: Cin, dgrad: Cout (weight column stride per tap); wgrad: Cout (row mask)
   int n_total;             // total N of the GEMM (fprop: Cout, dgrad: Cin, wgrad: Cin)
-  long long out_base;      // element offset of pixel (0,0,0)
-  long long sN, sH, sW;    // output strides in elements (fprop/dgrad); wgrad: sN = row stride (T*Cin)
+  int num_classes;
+  int max_splits;          // grid.z (fprop/dgrad) — classes may use fewer
   int accumulate;          // epilogue adds `addend` (same addressing as out)
+  int atomic_out;          // wgrad split-K: red.add the fp32 tile straight into the (pre-zeroed) output
+  long long sN, sH, sW;    // output strides in elements (fprop/dgrad); wgrad: sN = row stride (T*Cin)
   uint32_t a_lbo, a_sbo, b_lbo, b_sbo;   // smem descriptor strides (bytes)
-  TapEntry taps[16];
+  ConvClass cls[4];
 };
 
 struct ConvMaps {
@@ -80,11 +92,17 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
   uint32_t* last_flag = tmem_ptr + 1;
 
   const int warp = threadIdx.x >> 5;
-  const int m_tile = blockIdx.x, n_tile = blockIdx.y;
+  int cid = 0;
+  if (MODE == MODE_DGRAD) {
+    while (cid + 1 < p.num_classes && (int)blockIdx.x >= p.cls[cid + 1].m_begin) ++cid;
+  }
+  const ConvClass& kc = p.cls[cid];
+  const int m_tile = blockIdx.x - kc.m_begin, n_tile = blockIdx.y;
   int split = blockIdx.z, tap_fixed = 0;
-  if (MODE == MODE_WGRAD) { tap_fixed = blockIdx.z / p.splits; split = blockIdx.z % p.splits; }
-  const int it_begin = split * p.iters_per_split;
-  const int it_end = min(it_begin + p.iters_per_split, p.iters_total);
+  if (MODE == MODE_WGRAD) { tap_fixed = blockIdx.z / kc.splits; split = blockIdx.z % kc.splits; }
+  if (split >= kc.splits) return;              // class with fewer splits than grid.z (whole CTA leaves)
+  const int it_begin = split * kc.iters_per_split;
+  const int it_end = min(it_begin + kc.iters_per_split, kc.iters_total);
   const int n0 = n_tile * BLOCK_N;
 
   if (warp == 0 && elect_one()) {
@@ -107,9 +125,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
 
   // pixel-tile coordinates (fprop/dgrad: the M tile; wgrad: decoded per K block)
   auto decode = [&](int t, int& w0, int& h0, int& nn0) {
-    int wt = t % p.tiles_w;
-    int ht = (t / p.tiles_w) % p.tiles_h;
-    int nt = t / (p.tiles_w * p.tiles_h);
+    int wt = t % kc.tiles_w;
+    int ht = (t / kc.tiles_w) % kc.tiles_h;
+    int nt = t / (kc.tiles_w * kc.tiles_h);
     w0 = wt * p.bw; h0 = ht * p.bh; nn0 = nt * p.bn;
   };
 
@@ -126,7 +144,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
         mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
         if (MODE == MODE_FPROP || MODE == MODE_DGRAD) {
           const int tap = it / p.kb_per_tap, kb = it - tap * p.kb_per_tap;
-          const TapEntry te = p.taps[tap];
+          const TapEntry te = kc.taps[tap];
           tma_load_4d(sA, &maps.act[te.map], &full_bar[stage], kb * 64, w0 + te.dw, h0 + te.dh, nn0);
           if (MODE == MODE_FPROP) {
             // weights [Cout rows][taps*Cin cols], K-major: one box of 64 cols x BLOCK_N rows
@@ -139,7 +157,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
           }
         } else {
           decode(it, w0, h0, nn0);
-          const TapEntry te = p.taps[tap_fixed];
+          const TapEntry te = kc.taps[tap_fixed];
           // A = dy[pix][co]  (MN-major, two 64-channel boxes) ; B = x[pix (+) tap][ci] (MN-major)
           tma_load_4d(sA, &maps.other, &full_bar[stage], m_tile * 128, w0, h0, nn0);
           tma_load_4d(sA + 8192, &maps.other, &full_bar[stage], m_tile * 128 + 64, w0, h0, nn0);
@@ -188,22 +206,30 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     long long row_off;
     if (MODE == MODE_WGRAD) {
       row_ok = (m_tile * 128 + row) < p.red_ch;   // Cout may be 64 (< one M tile)
-      row_off = p.out_base + (long long)(m_tile * 128 + row) * p.sN + (long long)p.taps[tap_fixed].wtap * p.n_total;
+      row_off = kc.out_base + (long long)(m_tile * 128 + row) * p.sN + (long long)kc.taps[tap_fixed].wtap * p.n_total;
     } else {
       int w0, h0, nn0;
       decode(m_tile, w0, h0, nn0);
       const int wl = row % p.bw, hl = (row / p.bw) % p.bh, nl = row / (p.bw * p.bh);
       const int w = w0 + wl, h = h0 + hl, n = nn0 + nl;
-      row_ok = (w < p.Wd) && (h < p.Hd) && (n < p.Nd);
-      row_off = p.out_base + n * p.sN + h * p.sH + w * p.sW;
+      row_ok = (w < kc.Wd) && (h < kc.Hd) && (n < p.Nd);
+      row_off = kc.out_base + n * p.sN + h * p.sH + w * p.sW;
     }
 
     auto emit = [&](int col0, const float (&v)[32]) {
       if (!row_ok) return;
       if (MODE == MODE_WGRAD) {
         float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + row_off + n0 + col0);
+        if (p.atomic_out && kc.splits > 1) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          for (int i = 0; i < 8; ++i)
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + i), "f"(v[4 * i]),
+                         "f"(v[4 * i + 1]), "f"(v[4 * i + 2]), "f"(v[4 * i + 3])
+                         : "memory");
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
       } else {
         __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + row_off + n0 + col0;
         const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(addend) + row_off + n0 + col0;
@@ -267,7 +293,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     };
 
     const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    if (p.splits == 1) {
+    if (kc.splits == 1 || (MODE == MODE_WGRAD && p.atomic_out)) {
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N; c += 32) {
         uint32_t r[32];
@@ -285,8 +311,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
       const int tiles_n = gridDim.y;
       const long long tile_lin = (MODE == MODE_WGRAD)
                                      ? ((long long)tap_fixed * gridDim.x + m_tile) * tiles_n + n_tile
-                                     : (long long)m_tile * tiles_n + n_tile;
-      float4* part = reinterpret_cast<float4*>(scratch) + (tile_lin * p.splits + split) * (BLOCK_N / 4) * 128;
+                                     : (long long)blockIdx.x * tiles_n + n_tile;
+      const int stride_splits = (MODE == MODE_WGRAD) ? kc.splits : p.max_splits;
+      float4* part = reinterpret_cast<float4*>(scratch) + (tile_lin * stride_splits + split) * (BLOCK_N / 4) * 128;
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N; c += 32) {
         uint32_t r[32];
@@ -301,13 +328,13 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
       if (et == 0) {
         __threadfence();                       // one fence per CTA publishes every epilogue thread's partial
         const unsigned int old = atomicAdd(&tickets[tile_lin], 1u);
-        const unsigned int last = (old == static_cast<unsigned int>(p.splits - 1)) ? 1u : 0u;
+        const unsigned int last = (old == static_cast<unsigned int>(kc.splits - 1)) ? 1u : 0u;
         if (last) __threadfence();
         *last_flag = last;
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (*last_flag) {
-        const float4* base = reinterpret_cast<const float4*>(scratch) + tile_lin * p.splits * (BLOCK_N / 4) * 128;
+        const float4* base = reinterpret_cast<const float4*>(scratch) + tile_lin * stride_splits * (BLOCK_N / 4) * 128;
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N; c += 32) {
           float v[32];
@@ -315,7 +342,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
           for (int i = 0; i < 32; ++i) v[i] = 0.f;
           // fixed summation order; 4 splits x 8 vectors in flight per thread
           int s = 0;
-          for (; s + 4 <= p.splits; s += 4) {
+          for (; s + 4 <= kc.splits; s += 4) {
             float4 t[4][8];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
@@ -330,7 +357,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
                 v[4 * i] += t[u][i].x; v[4 * i + 1] += t[u][i].y; v[4 * i + 2] += t[u][i].z; v[4 * i + 3] += t[u][i].w;
               }
           }
-          for (; s < p.splits; ++s) {
+          for (; s < kc.splits; ++s) {
             const float4* ps = base + (long long)s * (BLOCK_N / 4) * 128;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {

@@ -38,11 +38,16 @@ typedef struct {
   float* scratch;      /* split-K partial tiles (see ldnn_conv_query)                      */
   unsigned int* tickets; /* split-K arrival counters, zero-initialised once                */
   unsigned int a_lbo, a_sbo, b_lbo, b_sbo; /* debug: override smem-descriptor strides (0 = default) */
+  int atomic_out;      /* wgrad: split-K partial tiles are red.add'ed straight into dw (caller zeroes dw
+                          once per step) instead of going through scratch + ticket; not bit-reproducible */
   float* bn_sums;      /* fprop, optional: fp32 [2][Cout]; the epilogue ADDS per-channel sum and sum of
                           squares of the output (fused BN statistics); caller zeroes it per step        */
 } ldnn_conv_desc;
 
-int ldnn_conv_query(const ldnn_conv_desc* d, size_t* scratch_bytes, size_t* ticket_count, int* launches);
+/* sizes a plan needs; covered_classes (dgrad): how many of the stride^2 output parity classes receive any
+ * tap — fewer than stride^2 means part of dx is not written and the caller must pre-zero + accumulate */
+int ldnn_conv_query(const ldnn_conv_desc* d, size_t* scratch_bytes, size_t* ticket_count, int* launches,
+                    int* covered_classes);
 int ldnn_conv_plan_create(const ldnn_conv_desc* d, void** plan);
 int ldnn_conv_plan_run(void* plan, void* stream);
 void ldnn_conv_plan_destroy(void* plan);

@@ -281,7 +281,8 @@ class _StepPlan:
                 if u.src != "x":
                     descs.append((K.DGRAD, geo))
         ws = K.Workspace(dev)
-        ws.reserve(max(K.conv_query(m, *g)[0] for m, g in descs))
+        atomic = not eng.deterministic
+        ws.reserve(max(K.conv_query(m, *g, atomic_out=(atomic and m == K.WGRAD))[0] for m, g in descs))
         self.ws = ws
         partial_max = 0
         for u in spec.conv_units():
@@ -291,6 +292,8 @@ class _StepPlan:
         self.bn_ticket = torch.zeros(4, dtype=torch.int32, device=dev)
 
         # ---- forward ----
+        self.zero_ranges = []          # flat-grad ranges that atomic split-K wgrads accumulate into
+        zero_slot = len(self.ops)
         if self.training and not eng.deterministic:
             self._add(lambda: eng.bn_sums.zero_())
         for u in spec.units:
@@ -324,6 +327,17 @@ class _StepPlan:
                 self._add(lambda xs=xs, ys=ys, dys=dys, dxs=dxs, H=H, Wd=Wd, Cc=Cc, u=u: K.maxpool_bwd(
                     xs, ys, dys, dxs, n, H, Wd, Cc, u.k, u.stride, u.pad))
                 written.add(u.src)
+        # one memset per merged range (ranges of neighbouring layers are fused across small gaps)
+        merged = []
+        for a, b in sorted(self.zero_ranges):
+            if merged and a - merged[-1][1] <= (1 << 16):
+                merged[-1][1] = max(merged[-1][1], b)
+            else:
+                merged.append([a, b])
+        for a, b in merged:
+            view = fl.grads[a:b]
+            self.ops.insert(zero_slot, view.zero_)
+            self.num_launches += 1
 
     def _fwd_unit(self, u: ConvBN, W, P):
         eng, n = self.eng, self.n
@@ -399,15 +413,18 @@ class _StepPlan:
         else:
             geo = (n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad)
             xin = self.act[u.src]
-        wg = K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, workspace=self.ws)
+        atomic = not eng.deterministic
+        wg = K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, workspace=self.ws, atomic_out=atomic)
+        if atomic and K.conv_query(K.WGRAD, *geo)[0] > 0:        # split-K → red.add into a zeroed slice
+            sl = eng.flat.by_key[u.conv_key + ".weight"]
+            self.zero_ranges.append((sl.offset, sl.offset + sl.numel))
         self._add(wg.run, wg.num_launches)
         if u.src == "x":
             return
         dx = self.dact[u.src]
         acc = u.src in written
         # strided 1x1 dgrads leave parity classes untouched: start from zero and accumulate
-        _, _, nl = K.conv_query(K.DGRAD, *geo, accumulate=True)
-        full_cover = nl == u.stride * u.stride
+        full_cover = K.conv_query(K.DGRAD, *geo, accumulate=True)[3] == u.stride * u.stride
         if not acc and not full_cover:
             self._add(lambda: dx.zero_())
             acc = True

@@ -23,7 +23,8 @@ class ConvPlan:
     def __init__(self, mode: int, N: int, H: int, W: int, Cin: int, Cout: int, R: int, stride: int, pad: int,
                  x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, dw: Optional[torch.Tensor] = None,
                  addend: Optional[torch.Tensor] = None, accumulate: bool = False, block_n: int = 0, splits: int = 0,
-                 workspace=None, desc_override=None, bn_sums: Optional[torch.Tensor] = None):
+                 workspace=None, desc_override=None, bn_sums: Optional[torch.Tensor] = None,
+                 atomic_out: bool = False):
         d = L.ConvDesc()
         d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
         d.block_n, d.splits, d.accumulate = block_n, splits, int(accumulate)
@@ -31,10 +32,11 @@ class ConvPlan:
         d.dw = 0 if dw is None else dw.data_ptr()
         d.addend = 0 if addend is None else addend.data_ptr()
         d.bn_sums = 0 if bn_sums is None else bn_sums.data_ptr()
+        d.atomic_out = int(atomic_out)
         if desc_override:
             d.a_lbo, d.a_sbo, d.b_lbo, d.b_sbo = desc_override
-        sb, tk, nl = C.c_size_t(0), C.c_size_t(0), C.c_int(0)
-        L.check(L.lib().ldnn_conv_query(C.byref(d), C.byref(sb), C.byref(tk), C.byref(nl)))
+        sb, tk, nl, cc = C.c_size_t(0), C.c_size_t(0), C.c_int(0), C.c_int(0)
+        L.check(L.lib().ldnn_conv_query(C.byref(d), C.byref(sb), C.byref(tk), C.byref(nl), C.byref(cc)))
         self.scratch_bytes, self.ticket_count, self.num_launches = sb.value, tk.value, nl.value
         self._keep = [x, w, y, dw, addend, bn_sums]
         if sb.value:
@@ -83,13 +85,14 @@ class Workspace:
         self.scratch = torch.empty(max(self.need // 4, 1), dtype=torch.float32, device=self.device)
 
 
-def conv_query(mode, N, H, W, Cin, Cout, R, stride, pad, block_n=0, splits=0, accumulate=True):
+def conv_query(mode, N, H, W, Cin, Cout, R, stride, pad, block_n=0, splits=0, accumulate=True, atomic_out=False):
+    """(scratch bytes, ticket count, launches, covered dgrad parity classes)."""
     d = L.ConvDesc()
     d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
-    d.block_n, d.splits, d.accumulate = block_n, splits, int(accumulate)
-    sb, tk, nl = C.c_size_t(0), C.c_size_t(0), C.c_int(0)
-    L.check(L.lib().ldnn_conv_query(C.byref(d), C.byref(sb), C.byref(tk), C.byref(nl)))
-    return sb.value, tk.value, nl.value
+    d.block_n, d.splits, d.accumulate, d.atomic_out = block_n, splits, int(accumulate), int(atomic_out)
+    sb, tk, nl, cc = C.c_size_t(0), C.c_size_t(0), C.c_int(0), C.c_int(0)
+    L.check(L.lib().ldnn_conv_query(C.byref(d), C.byref(sb), C.byref(tk), C.byref(nl), C.byref(cc)))
+    return sb.value, tk.value, nl.value, cc.value
 
 
 def im2col_stem(x_nchw_f32, col_bf16, N, Cc, H, W, R, stride, pad, Kpad):

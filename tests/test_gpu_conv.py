@@ -40,7 +40,8 @@ def _run(case, mode, **kw):
         K.ConvPlan(K.DGRAD, N, H, W, Cin, Cout, R, s, p, dx, w.view(Cout, -1), dy, addend=dx, accumulate=True, **kw).run()
         torch.cuda.synchronize()
         return rel_err(dx, dx_ref)
-    dw = torch.full((Cout, R * R * Cin), float("nan"), device="cuda", dtype=torch.float32)
+    fill = 0.0 if kw.get("atomic_out") else float("nan")
+    dw = torch.full((Cout, R * R * Cin), fill, device="cuda", dtype=torch.float32)
     K.ConvPlan(K.WGRAD, N, H, W, Cin, Cout, R, s, p, x, None, dy, dw=dw, **kw).run()
     torch.cuda.synchronize()
     return rel_err(dw.view(Cout, R, R, Cin), dw_ref)
@@ -62,6 +63,13 @@ def test_dgrad(case):
 def test_wgrad(case):
     from ldnn_b200.ops import native_ops as K
     assert _run(case, K.WGRAD) < 5e-3
+
+
+@pytest.mark.parametrize("case", ENHANCED[:6] + ODD[:3])
+def test_wgrad_atomic_split_k(case):
+    """split-K partial tiles red.add'ed into a pre-zeroed dw (the engine's fast path)."""
+    from ldnn_b200.ops import native_ops as K
+    assert _run(case, K.WGRAD, atomic_out=True) < 5e-3
 
 
 @pytest.mark.parametrize("splits", [1, 2, 5])

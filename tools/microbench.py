@@ -40,8 +40,10 @@ if which in ("all", "bn"):
         dyr = torch.empty_like(y)
         t1 = graph_timeit(lambda: K.bn_fwd_stats(y, M, C, chunks, partial, ticket, gamma, beta, rm, rv, nbt, sm, si, sc, sh))
         t2 = graph_timeit(lambda: K.bn_fwd_apply(y, sc, sh, None, out, M, C, True))
-        t3 = graph_timeit(lambda: K.bn_bwd_reduce(dout, out, y, sm, si, partial, ticket[1:], M, C, chunks, True, dg, db))
-        t4 = graph_timeit(lambda: K.bn_bwd_apply(dout, out, y, sm, si, gamma, dg, db, dyr, None, M, C, True, False))
+        sums = torch.zeros(2 * C, device=dev)
+        t2 = graph_timeit(lambda: K.bn_fwd_apply_sums(y, sums, gamma, beta, rm, rv, nbt, sm, si, None, out, M, C, True, True))
+        t3 = graph_timeit(lambda: K.bn_bwd_reduce_sums(dout, out, y, sm, si, sums, M, C, chunks, True))
+        t4 = graph_timeit(lambda: K.bn_bwd_apply_sums(dout, out, y, sm, si, gamma, sums, dyr, None, dg, db, M, C, True, False))
         print(f"M={M:6d} C={C:5d} chunks={chunks:4d} stats {t1:6.1f} apply {t2:6.1f} bwd_reduce {t3:6.1f} bwd_apply {t4:6.1f}")
 if which in ("all", "conv"):
     print("== conv (us, graph-replayed): fprop dgrad wgrad   [TFLOP/s of fprop]")
@@ -56,7 +58,7 @@ if which in ("all", "conv"):
         dw = torch.empty(Cout, R * R * Cin, device="cuda", dtype=torch.float32)
         pf = K.ConvPlan(K.FPROP, N, H, W, Cin, Cout, R, s, p, x, w.view(Cout, -1), y)
         pd = K.ConvPlan(K.DGRAD, N, H, W, Cin, Cout, R, s, p, dx, w.view(Cout, -1), dy, addend=dx, accumulate=True)
-        pw = K.ConvPlan(K.WGRAD, N, H, W, Cin, Cout, R, s, p, x, None, dy, dw=dw)
+        pw = K.ConvPlan(K.WGRAD, N, H, W, Cin, Cout, R, s, p, x, None, dy, dw=dw, atomic_out=True)
         tf, td, tw = graph_timeit(pf.run), graph_timeit(pd.run), graph_timeit(pw.run)
         fl = 2.0 * N * P * Q * Cout * R * R * Cin
         print(f"{str(case):40s} {tf:6.1f} {td:6.1f} {tw:6.1f}   [{fl / tf / 1e6:6.1f}]  launches f/d/w {pf.num_launches}/{pd.num_launches}/{pw.num_launches}")
