@@ -234,31 +234,43 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
         if (threadIdx.x == 0 && alive) alive = spin_until(x, prev_flags + fidx + (step - 1), seq + 2);
         __syncthreads();
       }
-      if (rs) {
-        for (long long i = lo + threadIdx.x; i < hi; i += kCommThreads) {
-          float4 in = ld_sys_f4(gp + i);
-          if (s == 0) in = f4_scale(in, e.weight[prev]);
-          float4 acc = f4_fma(gr[i], e.weight[r], in);
-          if (last_rs && update) {
-            float4 p0 = pr[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
-            optim_update4(p0, acc, m0, v0, e.opt);
-            pr[i] = p0; my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
-            if (cast) store_bf16x4(sh + 4 * i, p0);
-          } else {
-            gr[i] = acc;
-            if (last_rs && cast) store_bf16x4(sh + 4 * i, acc);
+      // 4 independent 16-byte peer loads in flight per thread (NVLink latency ~2.5 us: a single
+      // outstanding load per thread caps a CTA at a few GB/s)
+      constexpr int U = 4;
+      for (long long base = lo + threadIdx.x; base < hi; base += (long long)U * kCommThreads) {
+        float4 in[U], own[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long long i = base + (long long)u * kCommThreads;
+          if (i < hi) in[u] = ld_sys_f4((rs || !update ? gp : pp) + i);
+        }
+        if (rs) {
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const long long i = base + (long long)u * kCommThreads;
+            if (i < hi) own[u] = gr[i];
           }
         }
-      } else {
-        for (long long i = lo + threadIdx.x; i < hi; i += kCommThreads) {
-          if (update) {
-            const float4 v = ld_sys_f4(pp + i);
-            pr[i] = v;
-            if (cast) store_bf16x4(sh + 4 * i, v);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long long i = base + (long long)u * kCommThreads;
+          if (i >= hi) continue;
+          if (rs) {
+            float4 v = in[u];
+            if (s == 0) v = f4_scale(v, e.weight[prev]);
+            float4 acc = f4_fma(own[u], e.weight[r], v);
+            if (last_rs && update) {
+              float4 p0 = pr[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
+              optim_update4(p0, acc, m0, v0, e.opt);
+              pr[i] = p0; my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
+              if (cast) store_bf16x4(sh + 4 * i, p0);
+            } else {
+              gr[i] = acc;
+              if (last_rs && cast) store_bf16x4(sh + 4 * i, acc);
+            }
           } else {
-            const float4 v = ld_sys_f4(gp + i);
-            gr[i] = v;
-            if (cast) store_bf16x4(sh + 4 * i, v);
+            if (update) pr[i] = in[u]; else gr[i] = in[u];
+            if (cast) store_bf16x4(sh + 4 * i, in[u]);
           }
         }
       }
@@ -298,6 +310,7 @@ gossip_pull_kernel(const ldnn_comm c, const Peers bufs, const Peers recv, const 
   const float4* p1 = reinterpret_cast<const float4*>(bufs.p[((r - off1) % W + W) % W]);
   float4* out = reinterpret_cast<float4*>(recv.p[r]);
   const long long stride = (long long)x.blocks * kCommThreads;
+#pragma unroll 4
   for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n4; i += stride) {
     float4 acc = f4_scale(mine[i], c_self);
     if (n_off > 0) acc = f4_fma(ld_sys_f4(p0 + i), c0, acc);
@@ -319,7 +332,13 @@ broadcast_kernel(const ldnn_comm c, const Peers bufs, const long long n16, const
     const float4* s = reinterpret_cast<const float4*>(bufs.p[src]);
     float4* d = reinterpret_cast<float4*>(bufs.p[x.rank]);
     const long long stride = (long long)x.blocks * kCommThreads;
-    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n16; i += stride) d[i] = ld_sys_f4(s + i);
+    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n16; i += 4 * stride) {
+      float4 t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (i + u * stride < n16) t[u] = ld_sys_f4(s + i + u * stride);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (i + u * stride < n16) d[i + u * stride] = t[u];
+    }
   }
   comm_barrier(x, seq + 2);
 }

@@ -62,6 +62,7 @@ class NativeEngine(Engine):
         # BN statistics: fused into the conv epilogue with fp32 red.add (fast, summation order not
         # fixed) or the ticketed two-level reduction (bit-reproducible, ~2x more launches).
         self.deterministic = bool(os.environ.get("LDNN_DETERMINISTIC"))
+        self.bucket_elems = int(os.environ.get("LDNN_BUCKET_MB", "32")) * (1 << 20) // 4
         torch.cuda.set_device(self.device)
         # ---- geometry ------------------------------------------------------------
         self.info: Dict[str, _ConvInfo] = {}
@@ -198,6 +199,15 @@ class NativeEngine(Engine):
             self.local_update()
         return p.loss[0], p.correct[0]
 
+    def train_step_sync(self, x, y, exchanger):
+        """Product schedule (--sync step): forward/backward with the fused exchange+update of each
+        gradient bucket overlapped with the rest of backward (BASELINE north star)."""
+        p = self._plan(int(x.shape[0]), True)
+        exchanger.begin_step(self)
+        p.run_bucketed(x, y, lambda lo, hi: exchanger.exchange_bucket(self, lo, hi))
+        exchanger.end_step(self)
+        return p.loss[0], p.correct[0]
+
     def local_update(self) -> None:
         f = self.flat
         f.step += 1
@@ -252,6 +262,7 @@ class _StepPlan:
         self.num_launches = 0
         self._build()
         self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.seg_graphs: Optional[List[torch.cuda.CUDAGraph]] = None
         self._warm = False
 
     # -- helpers -----------------------------------------------------------------
@@ -316,10 +327,30 @@ class _StepPlan:
         if not self.training:
             return
         # ---- backward ----
+        # Buckets for the overlapped exchange: flat grads are laid out in forward order and produced in
+        # reverse, so finished gradients always form a suffix [lo, total); a bucket closes at a residual
+        # block boundary once it holds >= bucket_elems elements.
+        self.bucket_marks = []           # (number of ops enqueued so far, lo, hi)
+        done_keys = {spec.head().fc_key + ".weight", spec.head().fc_key + ".bias"}
+        prev_lo = fl.total
+
+        def close_bucket(force=False):
+            nonlocal prev_lo
+            lo = fl.total
+            for sl in reversed(fl.slots):            # longest finished suffix
+                if sl.key not in done_keys:
+                    break
+                lo = sl.offset
+            if lo < prev_lo and (force or prev_lo - lo >= eng.bucket_elems):
+                self.bucket_marks.append((len(self.ops), lo, prev_lo))
+                prev_lo = lo
+
         written = {spec.head().src}      # slots whose gradient buffer already holds a contribution
         for u in reversed(spec.units):
             if isinstance(u, ConvBN):
                 self._bwd_unit(u, W, P, G, written)
+                done_keys.update({u.conv_key + ".weight", u.bn_key + ".weight", u.bn_key + ".bias"})
+                close_bucket()
             elif isinstance(u, MaxPool):
                 H, Wd, Cc = eng.slot_shape[u.src]
                 assert u.src not in written, "max-pool input with gradient fan-in is not supported"
@@ -327,6 +358,8 @@ class _StepPlan:
                 self._add(lambda xs=xs, ys=ys, dys=dys, dxs=dxs, H=H, Wd=Wd, Cc=Cc, u=u: K.maxpool_bwd(
                     xs, ys, dys, dxs, n, H, Wd, Cc, u.k, u.stride, u.pad))
                 written.add(u.src)
+        close_bucket(force=True)
+        assert prev_lo == 0, "backward did not produce every gradient"
         # one memset per merged range (ranges of neighbouring layers are fused across small gaps)
         merged = []
         for a, b in sorted(self.zero_ranges):
@@ -338,6 +371,7 @@ class _StepPlan:
             view = fl.grads[a:b]
             self.ops.insert(zero_slot, view.zero_)
             self.num_launches += 1
+            self.bucket_marks = [(k + 1, lo, hi) for k, lo, hi in self.bucket_marks]
 
     def _fwd_unit(self, u: ConvBN, W, P):
         eng, n = self.eng, self.n
@@ -436,6 +470,36 @@ class _StepPlan:
     def _launch_all(self):
         for fn in self.ops:
             fn()
+
+    def run_bucketed(self, x: torch.Tensor, y: torch.Tensor, on_bucket):
+        """Same step, cut into one CUDA graph per bucket: after segment k is enqueued,
+        ``on_bucket(lo, hi)`` is called so the exchange of that flat-grad range can start on a side
+        stream while segment k+1 (the rest of backward) runs."""
+        self.x_in.copy_(x, non_blocking=True)
+        self.labels.copy_(y, non_blocking=True)
+        bounds = [0] + [k for k, _, _ in self.bucket_marks]
+        if not self._warm:
+            self._launch_all()
+            torch.cuda.current_stream().synchronize()
+            self._warm = True
+            for _, lo, hi in self.bucket_marks:
+                on_bucket(lo, hi)
+            return
+        if self.seg_graphs is None and self.eng.use_graph:
+            self.seg_graphs = []
+            for a, b in zip(bounds[:-1], bounds[1:]):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    for fn in self.ops[a:b]:
+                        fn()
+                self.seg_graphs.append(g)
+        for i, (_, lo, hi) in enumerate(self.bucket_marks):
+            if self.eng.use_graph:
+                self.seg_graphs[i].replay()
+            else:
+                for fn in self.ops[bounds[i]:bounds[i + 1]]:
+                    fn()
+            on_bucket(lo, hi)
 
     def run(self, x: torch.Tensor, y: torch.Tensor):
         self.x_in.copy_(x, non_blocking=True)

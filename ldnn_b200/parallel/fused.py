@@ -110,18 +110,20 @@ class FusedExchanger:
     def set_shard_weights(self, w) -> None:
         self.spec.shard_weights = list(w)
 
-    def _exchange_struct(self, data: str, mode: int, opt=None) -> L.Exchange:
+    def _exchange_struct(self, data: str, mode: int, opt=None, lo: int = 0, hi: Optional[int] = None) -> L.Exchange:
+        """Exchange descriptor for flat elements [lo, hi) (a bucket) — the whole slab by default."""
+        hi = self.n if hi is None else hi
         e = L.Exchange()
         tab = self._bufs[data].table()
         ptab = self._bufs["params"].table()
-        for i in range(L.MAX_RANKS):
-            e.grads[i], e.params[i] = tab[i], ptab[i]
+        for i in range(self.world):
+            e.grads[i], e.params[i] = tab[i] + 4 * lo, ptab[i] + 4 * lo
         f = self.engine.flat
-        e.m = f.m.data_ptr() if f.m is not None else 0
-        e.v = f.v.data_ptr() if f.v is not None else 0
+        e.m = f.m.data_ptr() + 4 * lo if f.m is not None else 0
+        e.v = f.v.data_ptr() + 4 * lo if f.v is not None else 0
         sh = getattr(self.engine, "shadow", None)
-        e.shadow = 0 if sh is None else sh.data_ptr()
-        e.n = self.n
+        e.shadow = 0 if sh is None else sh.data_ptr() + 2 * lo
+        e.n = hi - lo
         a, b = reduce_form(self.spec, self.rank)
         for i in range(self.world):
             e.weight[i] = b[i]
@@ -129,8 +131,8 @@ class FusedExchanger:
         if a != 0.0:
             mode |= L.X_SELFMIX
             rtab = self._recv_buf().table()
-            for i in range(L.MAX_RANKS):
-                e.recv[i] = rtab[i]
+            for i in range(self.world):
+                e.recv[i] = rtab[i] + 4 * lo
         e.mode = mode
         if opt is not None:
             e.opt = opt
@@ -172,6 +174,33 @@ class FusedExchanger:
         self._launch_reduce(e)
         if apply_update and getattr(engine, "shadow", None) is None:
             engine.params_changed()
+
+    # ------------------------------------------------------------------ bucketed, overlapped with backward
+    def begin_step(self, engine):
+        """Start an overlapped step: fixes the optimizer scalars for every bucket of this step."""
+        f = engine.flat
+        f.step += 1
+        self._step_opt = L.make_optim(f.opt, f.step, f.lr)
+        if not hasattr(self, "_comm_stream"):
+            self._comm_stream = torch.cuda.Stream(self.rt.device, priority=-1)
+
+    def exchange_bucket(self, engine, lo: int, hi: int) -> None:
+        """Called right after the backward kernels that complete flat-grad range [lo, hi) were
+        enqueued on the current stream: the fused exchange+update for that bucket runs on the
+        high-priority comm stream while backward continues."""
+        main = torch.cuda.current_stream(self.rt.device)
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self._comm_stream.wait_event(ev)
+        with torch.cuda.stream(self._comm_stream):
+            e = self._exchange_struct("grads", L.X_UPDATE, self._step_opt, lo, hi)
+            self._launch_reduce(e)
+
+    def end_step(self, engine) -> None:
+        """The next forward needs every bucket's updated parameters."""
+        ev = torch.cuda.Event()
+        ev.record(self._comm_stream)
+        torch.cuda.current_stream(self.rt.device).wait_event(ev)
 
     def exchange_weights(self, engine) -> None:
         if self.spec.is_gossip():

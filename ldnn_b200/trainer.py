@@ -114,8 +114,12 @@ def train_local_epoch(engine, loader: D.Loader, rt, exchanger=None, sync_step: b
             if i >= n_steps:
                 break
             if sync_step and exchanger is not None:
-                loss, corr = engine.train_step(x, y, update=False)
-                exchanger.exchange_grads(engine, apply_update=True)
+                if hasattr(engine, "train_step_sync") and hasattr(exchanger, "exchange_bucket") \
+                        and not exchanger.spec.is_gossip():
+                    loss, corr = engine.train_step_sync(x, y, exchanger)      # bucketed, overlapped
+                else:
+                    loss, corr = engine.train_step(x, y, update=False)
+                    exchanger.exchange_grads(engine, apply_update=True)
             else:
                 loss, corr = engine.train_step(x, y, update=True)
             losses[i] = loss
