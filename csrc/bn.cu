@@ -271,13 +271,13 @@ __global__ void __launch_bounds__(256)
 bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ sums,
                      const float* __restrict__ gamma, const float* __restrict__ beta, float* running_mean,
                      float* running_var, long long* nbt, float* save_mean, float* save_invstd,
-                     const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out, long long total8, int C,
-                     int M, int relu, int training, float eps, float momentum) {
-  extern __shared__ float sm[];
-  float* s_scale = sm;
-  float* s_shift = sm + C;
+                     const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out, int rows_per_chunk,
+                     int C, int M, int relu, int training, float eps, float momentum) {
+  // CTA = (64-channel slab, row chunk): only this slab's 64 coefficients are derived in the prologue
+  __shared__ float s_scale[kSlab], s_shift[kSlab];
   const float inv_m = 1.f / (float)M;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  if (threadIdx.x < kSlab) {
+    const int c = blockIdx.x * kSlab + threadIdx.x;
     float mean, var;
     if (training) {
       mean = sums[c] * inv_m;
@@ -288,9 +288,9 @@ bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ y, const float* __restric
     }
     const float invstd = rsqrtf(var + eps);
     const float g = gamma[c];
-    s_scale[c] = g * invstd;
-    s_shift[c] = beta[c] - mean * g * invstd;
-    if (training && blockIdx.x == 0) {
+    s_scale[threadIdx.x] = g * invstd;
+    s_shift[threadIdx.x] = beta[c] - mean * g * invstd;
+    if (training && blockIdx.y == 0) {
       save_mean[c] = mean;
       save_invstd[c] = invstd;
       const float unbiased = (M > 1) ? var * (float)M / (float)(M - 1) : var;
@@ -298,27 +298,31 @@ bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ y, const float* __restric
       running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
     }
   }
-  if (training && blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
+  if (training && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
   __syncthreads();
-  const int c8 = C >> 3;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total8;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % c8) * 8;
+  Lanes L;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { sc[k] = s_scale[L.cg * 8 + k]; sh[k] = s_shift[L.cg * 8 + k]; }
+  const int r0 = blockIdx.y * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
+#pragma unroll 4
+  for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
+    const size_t off = (size_t)r * C + L.c0;
     float f[8];
-    bf16x8_to_float(reinterpret_cast<const uint4*>(y)[i], f);
+    bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), f);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) f[k] = f[k] * s_scale[c0 + k] + s_shift[c0 + k];
+    for (int k = 0; k < 8; ++k) f[k] = f[k] * sc[k] + sh[k];
     if (res) {
-      float r[8];
-      bf16x8_to_float(reinterpret_cast<const uint4*>(res)[i], r);
+      float rr[8];
+      bf16x8_to_float(*reinterpret_cast<const uint4*>(res + off), rr);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) f[k] += r[k];
+      for (int k = 0; k < 8; ++k) f[k] += rr[k];
     }
     if (relu) {
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
     }
-    reinterpret_cast<uint4*>(out)[i] = float_to_bf16x8(f);
+    *reinterpret_cast<uint4*>(out + off) = float_to_bf16x8(f);
   }
 }
 
@@ -368,52 +372,52 @@ bn_bwd_apply_sums_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bflo
                          const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
                          const float* __restrict__ invstd, const float* __restrict__ gamma,
                          const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy_raw,
-                         __nv_bfloat16* __restrict__ dres, float* dgamma, float* dbeta, long long total8, int C,
-                         int relu, int res_accumulate, float inv_m) {
-  extern __shared__ float sm[];
-  float* s_mean = sm;            // mean
-  float* s_is = sm + C;          // invstd
-  float* s_k = sm + 2 * C;       // gamma*invstd
-  float* s_b = sm + 3 * C;       // dbeta/M
-  float* s_g = sm + 4 * C;       // dgamma/M
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+                         __nv_bfloat16* __restrict__ dres, float* dgamma, float* dbeta, int rows_per_chunk, int M,
+                         int C, int relu, int res_accumulate, float inv_m) {
+  __shared__ float s_co[5][kSlab];     // mean | invstd | gamma*invstd | dbeta/M | dgamma/M  (this slab)
+  if (threadIdx.x < kSlab) {
+    const int c = blockIdx.x * kSlab + threadIdx.x;
     const float is = invstd[c], db = sums[c], dg = sums[C + c];
-    s_mean[c] = mean[c]; s_is[c] = is; s_k[c] = gamma[c] * is; s_b[c] = db * inv_m; s_g[c] = dg * inv_m;
-    if (blockIdx.x == 0) { dbeta[c] = db; dgamma[c] = dg; }
+    s_co[0][threadIdx.x] = mean[c]; s_co[1][threadIdx.x] = is; s_co[2][threadIdx.x] = gamma[c] * is;
+    s_co[3][threadIdx.x] = db * inv_m; s_co[4][threadIdx.x] = dg * inv_m;
+    if (blockIdx.y == 0) { dbeta[c] = db; dgamma[c] = dg; }
   }
   __syncthreads();
-  const int c8 = C >> 3;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total8;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % c8) * 8;
+  Lanes L;
+  float mu[8], is[8], kk[8], kb[8], kg[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int j = L.cg * 8 + k;
+    mu[k] = s_co[0][j]; is[k] = s_co[1][j]; kk[k] = s_co[2][j]; kb[k] = s_co[3][j]; kg[k] = s_co[4][j];
+  }
+  const int r0 = blockIdx.y * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
+#pragma unroll 2
+  for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
+    const size_t off = (size_t)r * C + L.c0;
     float g[8], yy[8];
-    bf16x8_to_float(reinterpret_cast<const uint4*>(dout)[i], g);
-    bf16x8_to_float(reinterpret_cast<const uint4*>(y)[i], yy);
+    bf16x8_to_float(*reinterpret_cast<const uint4*>(dout + off), g);
+    bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), yy);
     if (relu) {
       float o[8];
-      bf16x8_to_float(reinterpret_cast<const uint4*>(outp)[i], o);
+      bf16x8_to_float(*reinterpret_cast<const uint4*>(outp + off), o);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] = (o[k] > 0.f) ? g[k] : 0.f;
     }
     if (dres) {
       if (res_accumulate) {
-        float r[8], t[8];
-        bf16x8_to_float(reinterpret_cast<const uint4*>(dres)[i], r);
+        float rr[8], t[8];
+        bf16x8_to_float(*reinterpret_cast<const uint4*>(dres + off), rr);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) t[k] = r[k] + g[k];
-        reinterpret_cast<uint4*>(dres)[i] = float_to_bf16x8(t);
+        for (int k = 0; k < 8; ++k) t[k] = rr[k] + g[k];
+        *reinterpret_cast<uint4*>(dres + off) = float_to_bf16x8(t);
       } else {
-        reinterpret_cast<uint4*>(dres)[i] = float_to_bf16x8(g);
+        *reinterpret_cast<uint4*>(dres + off) = float_to_bf16x8(g);
       }
     }
     float o8[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int c = c0 + k;
-      const float xh = (yy[k] - s_mean[c]) * s_is[c];
-      o8[k] = s_k[c] * (g[k] - s_b[c] - xh * s_g[c]);
-    }
-    reinterpret_cast<uint4*>(dy_raw)[i] = float_to_bf16x8(o8);
+    for (int k = 0; k < 8; ++k) o8[k] = kk[k] * (g[k] - kb[k] - (yy[k] - mu[k]) * is[k] * kg[k]);
+    *reinterpret_cast<uint4*>(dy_raw + off) = float_to_bf16x8(o8);
   }
 }
 
@@ -590,16 +594,22 @@ extern "C" int ldnn_bn_bwd_apply(const void* dout, const void* out, const void* 
   return LDNN_OK;
 }
 
+static int apply_chunks(int M, int C) {
+  // ~2-4 waves of CTAs over (C/64 slabs) x chunks, at least 32 rows (one pass of the row lanes) each
+  const int slabs = C / kSlab;
+  return std::max(1, std::min((M + 127) / 128, std::max(1, 592 / slabs)));
+}
+
 extern "C" int ldnn_bn_fwd_apply_sums(const void* y, const float* sums, const float* gamma, const float* beta,
                                       float* running_mean, float* running_var, long long* nbt, float* save_mean,
                                       float* save_invstd, const void* residual, void* out, int M, int C, int relu,
                                       int training, float eps, float momentum, void* stream) {
-  LDNN_ARG(C % 8 == 0 && C <= 4096, "bn: C=%d unsupported", C);
-  const long long total8 = (long long)M * C / 8;
-  const int blocks = (int)std::max(1LL, std::min<long long>((total8 + 1023) / 1024, 148 * 4));
-  bn_apply_sums_kernel<<<blocks, 256, 2 * C * sizeof(float), (cudaStream_t)stream>>>(
+  LDNN_ARG(C % kSlab == 0, "bn: C=%d unsupported (need C%%64==0)", C);
+  const int chunks = apply_chunks(M, C);
+  const int rows = (M + chunks - 1) / chunks;
+  bn_apply_sums_kernel<<<dim3(C / kSlab, chunks), 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)y, sums, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd,
-      (const __nv_bfloat16*)residual, (__nv_bfloat16*)out, total8, C, M, relu, training, eps, momentum);
+      (const __nv_bfloat16*)residual, (__nv_bfloat16*)out, rows, C, M, relu, training, eps, momentum);
   COUNT_LAUNCH();
   LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
@@ -622,12 +632,12 @@ extern "C" int ldnn_bn_bwd_apply_sums(const void* dout, const void* out, const v
                                       const float* save_invstd, const float* gamma, const float* sums, void* dy_raw,
                                       void* dres, float* dgamma, float* dbeta, int M, int C, int relu,
                                       int res_accumulate, void* stream) {
-  LDNN_ARG(C % 8 == 0 && C <= 2048, "bn: C=%d unsupported", C);
-  const long long total8 = (long long)M * C / 8;
-  const int blocks = (int)std::max(1LL, std::min<long long>((total8 + 1023) / 1024, 148 * 4));
-  bn_bwd_apply_sums_kernel<<<blocks, 256, 5 * C * sizeof(float), (cudaStream_t)stream>>>(
+  LDNN_ARG(C % kSlab == 0, "bn: C=%d unsupported (need C%%64==0)", C);
+  const int chunks = apply_chunks(M, C);
+  const int rows = (M + chunks - 1) / chunks;
+  bn_bwd_apply_sums_kernel<<<dim3(C / kSlab, chunks), 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, gamma,
-      sums, (__nv_bfloat16*)dy_raw, (__nv_bfloat16*)dres, dgamma, dbeta, total8, C, relu, res_accumulate,
+      sums, (__nv_bfloat16*)dy_raw, (__nv_bfloat16*)dres, dgamma, dbeta, rows, M, C, relu, res_accumulate,
       1.f / (float)M);
   COUNT_LAUNCH();
   LDNN_CUDA(cudaGetLastError());

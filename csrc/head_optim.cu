@@ -91,13 +91,31 @@ __global__ void __launch_bounds__(256)
 head_reduce_kernel(const float* __restrict__ pooled, const float* __restrict__ dlogits,
                    const float* __restrict__ loss_n, const float* __restrict__ correct_n, int N, int C, int classes,
                    float* __restrict__ dfc_w, float* __restrict__ dfc_b, float* __restrict__ loss_out,
-                   float* __restrict__ correct_out, int training) {
+                   float* __restrict__ correct_out, int training, int staged) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (training && c < C) {
-    for (int j = 0; j < classes; ++j) {
-      float s = 0.f;
-      for (int n = 0; n < N; ++n) s += dlogits[(size_t)n * classes + j] * pooled[(size_t)n * C + c];
-      dfc_w[(size_t)j * C + c] = s;
+  extern __shared__ float s_stage[];       // dlogits [N][classes] when it fits in smem
+  const float* s_dl = staged ? s_stage : dlogits;
+  if (training) {
+    if (staged) {
+      for (int i = threadIdx.x; i < N * classes; i += blockDim.x) s_stage[i] = dlogits[i];
+      __syncthreads();
+    }
+    if (c < C) {
+      // classes handled 8 at a time: pooled[n][c] is read once per group (coalesced over c)
+      for (int j0 = 0; j0 < classes; j0 += 8) {
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        for (int n = 0; n < N; ++n) {
+          const float pv = pooled[(size_t)n * C + c];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (j0 + j < classes) acc[j] += s_dl[n * classes + j0 + j] * pv;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j0 + j < classes) dfc_w[(size_t)(j0 + j) * C + c] = acc[j];
+      }
     }
   }
   if (blockIdx.x == 0) {
@@ -151,15 +169,17 @@ extern "C" int ldnn_head_fwd_bwd(const void* act, int N, int HW, int C, int clas
                                  float* dfc_w, float* dfc_b, float* loss_out, float* correct_out, int training,
                                  void* stream) {
   LDNN_ARG(C % 2 == 0 && classes <= kMaxClasses, "head: C=%d classes=%d", C, classes);
+  const size_t stage_bytes = (size_t)N * classes * sizeof(float);
+  const int staged = stage_bytes <= 40 * 1024;
   const size_t smem = (size_t)(C + 2 * classes) * sizeof(float);
   head_sample_kernel<<<N, 256, smem, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)act, HW, C, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,
       (__nv_bfloat16*)dact, training, 1.f / (float)N);
   g_launches.fetch_add(1);
   LDNN_CUDA(cudaGetLastError());
-  head_reduce_kernel<<<(C + 255) / 256, 256, 0, (cudaStream_t)stream>>>(pooled, dlogits, loss_n, correct_n, N, C,
+  head_reduce_kernel<<<(C + 127) / 128, 128, staged ? stage_bytes : 0, (cudaStream_t)stream>>>(pooled, dlogits, loss_n, correct_n, N, C,
                                                                        classes, dfc_w, dfc_b, loss_out, correct_out,
-                                                                       training);
+                                                                       training, staged);
   g_launches.fetch_add(1);
   LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
