@@ -112,7 +112,9 @@ def run_ours(a):
 
     epoch(max(a.warmup, 3))
     barrier_sync(dev)
-    l0 = L.launch_count() if L.available() else 0
+    def launches_now():
+        return (L.launch_count() if L.available() else 0) + getattr(engine, "graph_kernel_launches", 0)
+    l0 = launches_now()
     with ClockSampler(dev.index or 0) as clk:
         barrier_sync(dev)
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -121,7 +123,7 @@ def run_ours(a):
         t1.record()
         barrier_sync(dev)
         ms = t0.elapsed_time(t1)
-    launches = (L.launch_count() - l0) if L.available() else 0
+    launches = launches_now() - l0        # eager launches + kernels replayed from the step's CUDA graphs
     ms = max_over_ranks(ms, dev)
 
     # ---- end to end through the public API: pinned H2D of every batch, D2H of every loss ----

@@ -63,6 +63,13 @@ class NativeEngine(Engine):
         # fixed) or the ticketed two-level reduction (bit-reproducible, ~2x more launches).
         self.deterministic = bool(os.environ.get("LDNN_DETERMINISTIC"))
         self.bucket_elems = int(os.environ.get("LDNN_BUCKET_MB", "32")) * (1 << 20) // 4
+        # graph topology: wgrad runs on a side stream concurrently with the dgrad -> bn-backward chain
+        # (both only read dy_raw), and the local optimizer runs bucket by bucket on a third stream
+        # while backward continues.  Off in deterministic mode (shared split-K scratch).
+        self.concurrent = not self.deterministic and not os.environ.get("LDNN_SERIAL")
+        self._opt_stream = None
+        self.graph_kernel_launches = 0    # kernels launched through CUDA-graph replays (the library's
+                                          # own counter only sees eager launches)
         torch.cuda.set_device(self.device)
         # ---- geometry ------------------------------------------------------------
         self.info: Dict[str, _ConvInfo] = {}
@@ -194,10 +201,37 @@ class NativeEngine(Engine):
 
     def train_step(self, x, y, update: bool = True):
         p = self._plan(int(x.shape[0]), True)
-        p.run(x, y)
-        if update:
-            self.local_update()
+        if update and self.concurrent:
+            self._train_step_overlapped_update(p, x, y)
+        else:
+            p.run(x, y)
+            if update:
+                self.local_update()
         return p.loss[0], p.correct[0]
+
+    def _train_step_overlapped_update(self, p, x, y) -> None:
+        """Local schedule: the optimizer of each finished gradient bucket runs on its own stream while
+        the rest of backward is still executing (Adam is HBM-bound, backward is latency-bound)."""
+        f = self.flat
+        f.step += 1
+        o = L.make_optim(f.opt, f.step, f.lr)
+        if self._opt_stream is None:
+            self._opt_stream = torch.cuda.Stream(self.device)
+        main = torch.cuda.current_stream(self.device)
+        opt_stream = self._opt_stream
+
+        def on_bucket(lo, hi):
+            ev = torch.cuda.Event()
+            ev.record(main)
+            opt_stream.wait_event(ev)
+            with torch.cuda.stream(opt_stream):
+                K.optim_step(f.params[lo:hi], f.grads[lo:hi], f.m[lo:hi], None if f.v is None else f.v[lo:hi],
+                             self.shadow[lo:hi], hi - lo, o)
+
+        p.run_bucketed(x, y, on_bucket)
+        ev = torch.cuda.Event()
+        ev.record(opt_stream)
+        main.wait_event(ev)
 
     def train_step_sync(self, x, y, exchanger):
         """Product schedule (--sync step): forward/backward with the fused exchange+update of each
@@ -253,6 +287,12 @@ class _StepPlan:
             if ci.im2col:
                 self.col[u.conv_key] = bf(n, ci.P, ci.Q, ci.kdim)
         self.dy_raw = bf(max_raw) if training else None
+        self.dy_raw_unit = {}
+        if training and eng.concurrent:       # wgrad(k) on the side stream outlives unit k: private dy_raw per unit
+            for u in spec.conv_units():
+                ci = eng.info[u.conv_key]
+                self.dy_raw_unit[u.conv_key] = bf(n * ci.P * ci.Q * u.cout)
+        self.side = torch.cuda.Stream(dev) if (training and eng.concurrent) else None
         hd = spec.head()
         self.pooled, self.logits, self.dlogits = f32(n, hd.cin), f32(n, hd.num_classes), f32(n, hd.num_classes)
         self.loss_n, self.correct_n = f32(n), f32(n)
@@ -270,8 +310,8 @@ class _StepPlan:
         """Row chunks of the BN reductions: (C/64 channel slabs) x chunks CTAs, ~2 waves at most."""
         return max(1, min(M // 128, max(1, 296 // max(1, C // 64))))
 
-    def _add(self, fn, launches: int = 1):
-        self.ops.append(fn)
+    def _add(self, fn, launches: int = 1, side: bool = False):
+        self.ops.append((fn, side and self.side is not None))
         self.num_launches += launches
 
     def _build(self):
@@ -369,7 +409,7 @@ class _StepPlan:
                 merged.append([a, b])
         for a, b in merged:
             view = fl.grads[a:b]
-            self.ops.insert(zero_slot, view.zero_)
+            self.ops.insert(zero_slot, (view.zero_, False))
             self.num_launches += 1
             self.bucket_marks = [(k + 1, lo, hi) for k, lo, hi in self.bucket_marks]
 
@@ -423,7 +463,7 @@ class _StepPlan:
         gamma = P(u.bn_key + ".weight")
         dgamma, dbeta = G(u.bn_key + ".weight"), G(u.bn_key + ".bias")
         chunks = self._chunks(M, Cc)
-        dyr = self.dy_raw[:M * Cc]
+        dyr = self.dy_raw_unit.get(u.conv_key, self.dy_raw[:M * Cc])
         dres, res_acc = None, False
         if u.residual is not None:
             dres = self.dact[u.residual]
@@ -452,7 +492,7 @@ class _StepPlan:
         if atomic and K.conv_query(K.WGRAD, *geo)[0] > 0:        # split-K → red.add into a zeroed slice
             sl = eng.flat.by_key[u.conv_key + ".weight"]
             self.zero_ranges.append((sl.offset, sl.offset + sl.numel))
-        self._add(wg.run, wg.num_launches)
+        self._add(wg.run, wg.num_launches, side=True)
         if u.src == "x":
             return
         dx = self.dact[u.src]
@@ -467,39 +507,28 @@ class _StepPlan:
         written.add(u.src)
 
     # -- execution ---------------------------------------------------------------
-    def _launch_all(self):
-        for fn in self.ops:
-            fn()
-
-    def run_bucketed(self, x: torch.Tensor, y: torch.Tensor, on_bucket):
-        """Same step, cut into one CUDA graph per bucket: after segment k is enqueued,
-        ``on_bucket(lo, hi)`` is called so the exchange of that flat-grad range can start on a side
-        stream while segment k+1 (the rest of backward) runs."""
-        self.x_in.copy_(x, non_blocking=True)
-        self.labels.copy_(y, non_blocking=True)
-        bounds = [0] + [k for k, _, _ in self.bucket_marks]
-        if not self._warm:
-            self._launch_all()
-            torch.cuda.current_stream().synchronize()
-            self._warm = True
-            for _, lo, hi in self.bucket_marks:
-                on_bucket(lo, hi)
-            return
-        if self.seg_graphs is None and self.eng.use_graph:
-            self.seg_graphs = []
-            for a, b in zip(bounds[:-1], bounds[1:]):
-                g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
-                    for fn in self.ops[a:b]:
-                        fn()
-                self.seg_graphs.append(g)
-        for i, (_, lo, hi) in enumerate(self.bucket_marks):
-            if self.eng.use_graph:
-                self.seg_graphs[i].replay()
-            else:
-                for fn in self.ops[bounds[i]:bounds[i + 1]]:
+    def _launch_range(self, a: int, b: int):
+        """Enqueue ops[a:b]; side-stream ops fork after the preceding main-stream op and are joined
+        back at the end of the range (so a range is a self-contained graph segment)."""
+        main = torch.cuda.current_stream(self.eng.device)
+        forked = False
+        for fn, side in self.ops[a:b]:
+            if side:
+                ev = torch.cuda.Event()
+                ev.record(main)
+                self.side.wait_event(ev)
+                with torch.cuda.stream(self.side):
                     fn()
-            on_bucket(lo, hi)
+                forked = True
+            else:
+                fn()
+        if forked:
+            ev = torch.cuda.Event()
+            ev.record(self.side)
+            main.wait_event(ev)
+
+    def _launch_all(self):
+        self._launch_range(0, len(self.ops))
 
     def run(self, x: torch.Tensor, y: torch.Tensor):
         self.x_in.copy_(x, non_blocking=True)
@@ -519,3 +548,34 @@ class _StepPlan:
                 self._launch_all()
             self.graph = g
         self.graph.replay()
+        self.eng.graph_kernel_launches += self.num_launches
+
+    def run_bucketed(self, x: torch.Tensor, y: torch.Tensor, on_bucket):
+        """Same step, cut into one CUDA graph per bucket: after segment k is enqueued,
+        ``on_bucket(lo, hi)`` is called so the exchange / optimizer of that flat-grad range can start on
+        another stream while segment k+1 (the rest of backward) runs."""
+        self.x_in.copy_(x, non_blocking=True)
+        self.labels.copy_(y, non_blocking=True)
+        bounds = [0] + [k for k, _, _ in self.bucket_marks]
+        if not self._warm:
+            self._launch_all()
+            torch.cuda.current_stream().synchronize()
+            self._warm = True
+            for _, lo, hi in self.bucket_marks:
+                on_bucket(lo, hi)
+            return
+        if self.seg_graphs is None and self.eng.use_graph:
+            self.seg_graphs = []
+            for a, b in zip(bounds[:-1], bounds[1:]):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._launch_range(a, b)
+                self.seg_graphs.append(g)
+        for i, (_, lo, hi) in enumerate(self.bucket_marks):
+            if self.eng.use_graph:
+                self.seg_graphs[i].replay()
+            else:
+                self._launch_range(bounds[i], bounds[i + 1])
+            on_bucket(lo, hi)
+        if self.eng.use_graph:
+            self.eng.graph_kernel_launches += self.num_launches
