@@ -346,7 +346,7 @@ class _StepPlan:
         self.zero_ranges = []          # flat-grad ranges that atomic split-K wgrads accumulate into
         zero_slot = len(self.ops)
         if self.training and not eng.deterministic:
-            self._add(lambda: eng.bn_sums.zero_())
+            self._add(lambda: eng.bn_sums.zero_(), 0)          # memset node, not one of our kernels
         for u in spec.units:
             if isinstance(u, ConvBN):
                 self._fwd_unit(u, W, P)
@@ -410,7 +410,6 @@ class _StepPlan:
         for a, b in merged:
             view = fl.grads[a:b]
             self.ops.insert(zero_slot, (view.zero_, False))
-            self.num_launches += 1
             self.bucket_marks = [(k + 1, lo, hi) for k, lo, hi in self.bucket_marks]
 
     def _fwd_unit(self, u: ConvBN, W, P):
@@ -500,7 +499,7 @@ class _StepPlan:
         # strided 1x1 dgrads leave parity classes untouched: start from zero and accumulate
         full_cover = K.conv_query(K.DGRAD, *geo, accumulate=True)[3] == u.stride * u.stride
         if not acc and not full_cover:
-            self._add(lambda: dx.zero_())
+            self._add(lambda: dx.zero_(), 0)
             acc = True
         dg = K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx if acc else None, accumulate=acc, workspace=self.ws)
         self._add(dg.run, dg.num_launches)

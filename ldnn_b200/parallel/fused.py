@@ -228,6 +228,30 @@ class FusedExchanger:
         engine.params_changed()
         self.check()
 
+    # ------------------------------------------------------------------ K-MET: small all-gather
+    METRIC_CAP = 4096          # floats per rank
+
+    def allgather_floats(self, rec):
+        """Every rank's float record lands in slot [rank] of every peer's table (one P2P kernel;
+        replaces the reference's per-epoch scalar collectives C3-C5, C11, C13)."""
+        import numpy as np
+        n = int(len(rec))
+        if n > self.METRIC_CAP:
+            raise ValueError(f"metric record of {n} floats exceeds the table capacity {self.METRIC_CAP}")
+        if not hasattr(self, "_met"):
+            t, h, p = K.symm_alloc(self.world * self.METRIC_CAP * 4, self.rt.device)
+            self._met_t = t.view(torch.float32)
+            self._met = SymmetricBuffer("metrics", p, h, self.world * self.METRIC_CAP * 4, self.rt)
+            self._met_mine = torch.zeros(self.METRIC_CAP, dtype=torch.float32, device=self.rt.device)
+            if self.world > 1:
+                dist.barrier()
+        self._met_mine[:n].copy_(torch.as_tensor(np.asarray(rec, dtype=np.float32)), non_blocking=True)
+        c = self._comm()
+        L.check(L.lib().ldnn_allgather_small(C.byref(c), L.ptr(self._met_mine), self._met.table(), n, L.stream_ptr()))
+        self.launches += 1
+        torch.cuda.current_stream(self.rt.device).synchronize()
+        return self._met_t[: self.world * n].view(self.world, n).cpu().numpy()
+
     def barrier(self) -> None:
         c = self._comm()
         L.check(L.lib().ldnn_barrier(C.byref(c), L.stream_ptr()))

@@ -26,6 +26,7 @@ import torch
 import torch.distributed as dist
 
 from . import data as D
+from .utils.timing import nvtx_range
 
 
 @dataclass
@@ -62,8 +63,10 @@ class TrainHistory:
 class RecordGather:
     HEADER = 8  # [n_losses, train_loss, train_acc, val_loss, val_acc, finished, want_break, samples]
 
-    def __init__(self, rt):
+    def __init__(self, rt, exchanger=None):
         self.rt = rt
+        # on GPU the record all-gather is the K-MET P2P kernel; torch.distributed otherwise
+        self.p2p = exchanger if hasattr(exchanger, "allgather_floats") else None
 
     def max_int(self, v: int) -> int:
         if self.rt.world_size == 1:
@@ -88,6 +91,8 @@ class RecordGather:
         rec[self.HEADER:self.HEADER + len(losses)] = losses
         if self.rt.world_size == 1:
             return rec[None, :]
+        if self.p2p is not None and len(rec) <= self.p2p.METRIC_CAP:
+            return self.p2p.allgather_floats(rec)
         t = torch.from_numpy(rec).to(self._dev())
         out = [torch.empty_like(t) for _ in range(self.rt.world_size)]
         dist.all_gather(out, t)
@@ -208,7 +213,7 @@ def train_global(engine, bundle: D.DataBundle, shards: D.ShardState, cfg, rt, ex
     h = history or TrainHistory()
     if not h.all_workers_losses:
         h.all_workers_losses = [[] for _ in range(ws)]
-    g = RecordGather(rt)
+    g = RecordGather(rt, exchanger)
     rng = np.random.default_rng(None if cfg.seed is None else cfg.seed + 1000 + rank)
     sync_step = cfg.sync == "step"
 
@@ -224,9 +229,11 @@ def train_global(engine, bundle: D.DataBundle, shards: D.ShardState, cfg, rt, ex
         straggler_t0, samples = None, 0
 
         for le in range(cfg.epochs_local):
-            tl, ta, batch_losses, n = train_local_epoch(engine, train_loader, rt, exchanger, sync_step, steps)
+            with nvtx_range(f"train g{ge} l{le}"):
+                tl, ta, batch_losses, n = train_local_epoch(engine, train_loader, rt, exchanger, sync_step, steps)
             samples += n
-            vl, va = validate(engine, val_loader, rt)
+            with nvtx_range("validate"):
+                vl, va = validate(engine, val_loader, rt)
             want_break = 1.0 if (straggler_t0 is not None and time.time() - straggler_t0 > cfg.time_limit) else 0.0
             recs = g.gather([len(batch_losses), tl, ta, vl, va, 0.0, want_break, n], batch_losses, capacity)
             if rank == 0:
@@ -257,10 +264,11 @@ def train_global(engine, bundle: D.DataBundle, shards: D.ShardState, cfg, rt, ex
         # ---- the exchange (trainer.py:141-150) --------------------------------
         t_x = time.time()
         if not sync_step:
-            if cfg.aggregation_by == "gradients":
-                exchanger.exchange_grads(engine, apply_update=bool(cfg.apply_exchanged_grads))
-            else:
-                exchanger.exchange_weights(engine)
+            with nvtx_range("exchange"):
+                if cfg.aggregation_by == "gradients":
+                    exchanger.exchange_grads(engine, apply_update=bool(cfg.apply_exchanged_grads))
+                else:
+                    exchanger.exchange_weights(engine)
         if rt.is_cuda:
             torch.cuda.synchronize(rt.device)
         h.exchange_ms.append(1e3 * (time.time() - t_x))

@@ -16,6 +16,19 @@ import torch
 import torch.distributed as dist
 
 
+@contextmanager
+def nvtx_range(name: str):
+    """NVTX range around a phase (shows up in nsys/ncu timelines); no-op without CUDA."""
+    on = torch.cuda.is_available()
+    if on:
+        torch.cuda.nvtx.range_push(name)
+    try:
+        yield
+    finally:
+        if on:
+            torch.cuda.nvtx.range_pop()
+
+
 class CudaTimer:
     def __init__(self, device=None):
         self.device = device

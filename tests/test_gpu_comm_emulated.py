@@ -189,3 +189,16 @@ def test_broadcast_allgather_barrier_and_repeat():
         L.check(L.lib().ldnn_barrier(C.byref(c), None))
     emu.ok()
     assert all(torch.equal(t, mine) for t in tables)
+
+
+def test_watchdog_reports_a_missing_peer():
+    """Failure detection: a rank whose peer never arrives gets an error flag instead of a hung kernel
+    (upstream hangs forever in the next collective)."""
+    from ldnn_b200.ops import _lib as L
+    emu = Emu(2, 16)
+    c = emu.comm()
+    c.emulate, c.rank, c.blocks = 0, 0, 2         # real (non-emulated) rank 0 of 2; nobody plays rank 1
+    c.timeout_cycles = 60_000_000                # ~30 ms
+    L.check(L.lib().ldnn_barrier(C.byref(c), None))
+    torch.cuda.synchronize()
+    assert int(emu.err.item()) == 1
