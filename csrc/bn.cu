@@ -273,6 +273,8 @@ bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ y, const float* __restric
                      float* running_var, long long* nbt, float* save_mean, float* save_invstd,
                      const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out, int rows_per_chunk,
                      int C, int M, int relu, int training, float eps, float momentum) {
+  pdl_wait();
+  pdl_launch_dependents();
   // CTA = (64-channel slab, row chunk): only this slab's 64 coefficients are derived in the prologue
   __shared__ float s_scale[kSlab], s_shift[kSlab];
   const float inv_m = 1.f / (float)M;
@@ -331,6 +333,8 @@ bn_bwd_reduce_atomic_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_b
                             const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
                             const float* __restrict__ invstd, float* __restrict__ sums, int M, int C,
                             int rows_per_chunk, int relu) {
+  pdl_wait();
+  pdl_launch_dependents();
   __shared__ float smem[kRowLanes * 2 * kSlab];
   Lanes L;
   float a[8], b[8], mu[8], is[8];
@@ -374,6 +378,8 @@ bn_bwd_apply_sums_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bflo
                          const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy_raw,
                          __nv_bfloat16* __restrict__ dres, float* dgamma, float* dbeta, int rows_per_chunk, int M,
                          int C, int relu, int res_accumulate, float inv_m) {
+  pdl_wait();
+  pdl_launch_dependents();
   __shared__ float s_co[5][kSlab];     // mean | invstd | gamma*invstd | dbeta/M | dgamma/M  (this slab)
   if (threadIdx.x < kSlab) {
     const int c = blockIdx.x * kSlab + threadIdx.x;
@@ -425,6 +431,8 @@ bn_bwd_apply_sums_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bflo
 __global__ void __launch_bounds__(256)
 im2col_stem_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col, int N, int C, int H, int W, int R,
                    int stride, int pad, int P, int Q, int Kpad) {
+  pdl_wait();
+  pdl_launch_dependents();
   // one thread per (pixel, 8 consecutive k)
   const int k8 = Kpad >> 3;
   const long long total = (long long)N * P * Q * k8;
@@ -607,11 +615,11 @@ extern "C" int ldnn_bn_fwd_apply_sums(const void* y, const float* sums, const fl
   LDNN_ARG(C % kSlab == 0, "bn: C=%d unsupported (need C%%64==0)", C);
   const int chunks = apply_chunks(M, C);
   const int rows = (M + chunks - 1) / chunks;
-  bn_apply_sums_kernel<<<dim3(C / kSlab, chunks), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)y, sums, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd,
-      (const __nv_bfloat16*)residual, (__nv_bfloat16*)out, rows, C, M, relu, training, eps, momentum);
+  LDNN_CUDA(launch_pdl(bn_apply_sums_kernel, dim3(C / kSlab, chunks), dim3(256), 0, (cudaStream_t)stream,
+                       (const __nv_bfloat16*)y, sums, gamma, beta, running_mean, running_var, nbt, save_mean,
+                       save_invstd, (const __nv_bfloat16*)residual, (__nv_bfloat16*)out, rows, C, M, relu, training, eps,
+                       momentum));
   COUNT_LAUNCH();
-  LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
 
@@ -620,11 +628,10 @@ extern "C" int ldnn_bn_bwd_reduce_sums(const void* dout, const void* out, const 
                                        void* stream) {
   LDNN_ARG(C % kSlab == 0, "bn: C=%d unsupported (need C%%64==0)", C);
   const int rows = (M + chunks - 1) / chunks;
-  bn_bwd_reduce_atomic_kernel<<<dim3(C / kSlab, chunks), kBnThreads, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, sums, M,
-      C, rows, relu);
+  LDNN_CUDA(launch_pdl(bn_bwd_reduce_atomic_kernel, dim3(C / kSlab, chunks), dim3(kBnThreads), 0, (cudaStream_t)stream,
+                       (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean,
+                       save_invstd, sums, M, C, rows, relu));
   COUNT_LAUNCH();
-  LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
 
@@ -635,12 +642,11 @@ extern "C" int ldnn_bn_bwd_apply_sums(const void* dout, const void* out, const v
   LDNN_ARG(C % kSlab == 0, "bn: C=%d unsupported (need C%%64==0)", C);
   const int chunks = apply_chunks(M, C);
   const int rows = (M + chunks - 1) / chunks;
-  bn_bwd_apply_sums_kernel<<<dim3(C / kSlab, chunks), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, gamma,
-      sums, (__nv_bfloat16*)dy_raw, (__nv_bfloat16*)dres, dgamma, dbeta, rows, M, C, relu, res_accumulate,
-      1.f / (float)M);
+  LDNN_CUDA(launch_pdl(bn_bwd_apply_sums_kernel, dim3(C / kSlab, chunks), dim3(256), 0, (cudaStream_t)stream,
+                       (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean,
+                       save_invstd, gamma, sums, (__nv_bfloat16*)dy_raw, (__nv_bfloat16*)dres, dgamma, dbeta, rows, M, C,
+                       relu, res_accumulate, 1.f / (float)M));
   COUNT_LAUNCH();
-  LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
 
@@ -649,10 +655,9 @@ extern "C" int ldnn_im2col_stem(const float* x, void* col, int N, int C, int H, 
   LDNN_ARG(Kpad % 64 == 0 && Kpad >= R * R * C, "im2col: Kpad=%d", Kpad);
   const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - R) / stride + 1;
   const long long total = (long long)N * P * Q * (Kpad / 8);
-  im2col_stem_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)col, N, C, H, W, R,
-                                                                           stride, pad, P, Q, Kpad);
+  LDNN_CUDA(launch_pdl(im2col_stem_kernel, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream, x,
+                       (__nv_bfloat16*)col, N, C, H, W, R, stride, pad, P, Q, Kpad));
   COUNT_LAUNCH();
-  LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
 

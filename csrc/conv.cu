@@ -1,6 +1,7 @@
 // Host side of the implicit-GEMM convolution: tensor-map construction, tiling / split-K
 // heuristics, launch plans.  Kernel: conv_gemm.cuh.
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 #include <mutex>
@@ -14,6 +15,12 @@ namespace ldnn {
 
 static thread_local char g_err[512] = "";
 std::atomic<unsigned long long> g_launches{0};
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("LDNN_PDL"); on = (e && e[0] == '0') ? 0 : 1; }
+  return on == 1;
+}
 
 void set_last_error(const char* fmt, ...) {
   va_list ap;
@@ -305,11 +312,10 @@ static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
                                    Cfg::kSmemBytes));
     configured = true;
   }
-  conv_gemm_kernel<MODE, BN><<<L.grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(
-      L.maps, L.p, pl.out, pl.addend, pl.scratch ? pl.scratch + L.scratch_off : nullptr,
-      pl.tickets ? pl.tickets + L.ticket_off : nullptr, pl.stats);
+  LDNN_CUDA(launch_pdl(conv_gemm_kernel<MODE, BN>, L.grid, dim3(Cfg::kThreads), (size_t)Cfg::kSmemBytes, st, L.maps, L.p,
+                       pl.out, pl.addend, pl.scratch ? pl.scratch + L.scratch_off : nullptr,
+                       pl.tickets ? pl.tickets + L.ticket_off : nullptr, pl.stats));
   g_launches.fetch_add(1, std::memory_order_relaxed);
-  LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
 

@@ -19,6 +19,7 @@
 // order, so results are deterministic and no memset / atomics on the output are needed.
 #pragma once
 #include "ptx.cuh"
+#include "common.cuh"
 
 namespace ldnn {
 
@@ -122,6 +123,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  // PDL: everything above overlapped the previous kernel's tail; from here on we touch its outputs
+  pdl_wait();
+  pdl_launch_dependents();
 
   // pixel-tile coordinates (fprop/dgrad: the M tile; wgrad: decoded per K block)
   auto decode = [&](int t, int& w0, int& h0, int& nn0) {

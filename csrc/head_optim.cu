@@ -20,6 +20,8 @@ head_sample_kernel(const __nv_bfloat16* __restrict__ act, int HW, int C, int cla
                    float* __restrict__ logits, float* __restrict__ dlogits, float* __restrict__ loss_n,
                    float* __restrict__ correct_n, long long* __restrict__ pred, __nv_bfloat16* __restrict__ dact,
                    int training, float inv_batch) {
+  pdl_wait();
+  pdl_launch_dependents();
   extern __shared__ float sm[];          // pooled[C] | logits[classes] | dl[classes]
   float* sp = sm;
   float* sl = sm + C;
@@ -92,6 +94,8 @@ head_reduce_kernel(const float* __restrict__ pooled, const float* __restrict__ d
                    const float* __restrict__ loss_n, const float* __restrict__ correct_n, int N, int C, int classes,
                    float* __restrict__ dfc_w, float* __restrict__ dfc_b, float* __restrict__ loss_out,
                    float* __restrict__ correct_out, int training, int staged) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   extern __shared__ float s_stage[];       // dlogits [N][classes] when it fits in smem
   const float* s_dl = staged ? s_stage : dlogits;
@@ -172,16 +176,14 @@ extern "C" int ldnn_head_fwd_bwd(const void* act, int N, int HW, int C, int clas
   const size_t stage_bytes = (size_t)N * classes * sizeof(float);
   const int staged = stage_bytes <= 40 * 1024;
   const size_t smem = (size_t)(C + 2 * classes) * sizeof(float);
-  head_sample_kernel<<<N, 256, smem, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)act, HW, C, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,
-      (__nv_bfloat16*)dact, training, 1.f / (float)N);
+  LDNN_CUDA(launch_pdl(head_sample_kernel, dim3(N), dim3(256), smem, (cudaStream_t)stream, (const __nv_bfloat16*)act, HW,
+                       C, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,
+                       (__nv_bfloat16*)dact, training, 1.f / (float)N));
   g_launches.fetch_add(1);
-  LDNN_CUDA(cudaGetLastError());
-  head_reduce_kernel<<<(C + 127) / 128, 128, staged ? stage_bytes : 0, (cudaStream_t)stream>>>(pooled, dlogits, loss_n, correct_n, N, C,
-                                                                       classes, dfc_w, dfc_b, loss_out, correct_out,
-                                                                       training, staged);
+  LDNN_CUDA(launch_pdl(head_reduce_kernel, dim3((C + 127) / 128), dim3(128), staged ? stage_bytes : (size_t)0,
+                       (cudaStream_t)stream, (const float*)pooled, (const float*)dlogits, (const float*)loss_n,
+                       (const float*)correct_n, N, C, classes, dfc_w, dfc_b, loss_out, correct_out, training, staged));
   g_launches.fetch_add(1);
-  LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
 
