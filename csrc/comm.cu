@@ -185,9 +185,19 @@ allreduce_fused_kernel(const ldnn_comm c, const ldnn_exchange e) {
 }
 
 // ================================================================== K-RING / K-DRING: RS + AG rings
-// Region k of the slab belongs to ring k; ring 0 rotates +1 (pull from r-1), ring 1 rotates -1.
-// Flags: sig[kBarWords + ((ring*J + j) * 16 + step)] on the *producer's* pad (readers poll the
-// producer's pad through the peer mapping).
+// Region k of the slab belongs to ring k; ring 0 rotates +1 (sends to r+1), ring 1 rotates -1.
+// PUSH design: every hop is local loads -> remote *stores* into the next rank's buffer, followed by a
+// release flag written into the next rank's signal pad; the consumer polls its OWN pad and reads the
+// payload from its OWN memory.  No load ever crosses NVLink, so the ring is not exposed to the ~2.5 us
+// peer-load latency (a pull ring needs megabytes of loads in flight to hide it).
+//
+// Message k of rank r (chunk indices mod W, written for direction +1; c0 = r):
+//   k = 0          : send w_r*g[c0]                                 -> next.recv[c0]
+//   1 <= k <= W-2  : wait(k-1); send recv[c] + w_r*g[c], c = c0-k   -> next.recv[c]
+//   k = W-1        : wait(W-2); c = c0+1 is fully reduced here: (optimizer) -> own slab, -> next slab
+//   W <= k <= 2W-3 : wait(k-1); forward the finished chunk c = c0-k+W from own slab -> next slab
+//   end            : wait(2W-3) (last chunk has landed), bf16 cast of what arrived
+// Flags: sig[kBarWords + ((ring*J + j) * 16 + k)] in the CONSUMER's pad, value = this call's sequence.
 __global__ void __launch_bounds__(kCommThreads, 1)
 ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings, const int J, const long long sub4) {
   const Ctx x = make_ctx(c);
@@ -197,87 +207,86 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
   const bool update = (e.mode & LDNN_X_UPDATE) != 0;
   const bool cast = e.shadow != nullptr && (update || (e.mode & 4));
 
-  comm_barrier(x, seq + 1);
+  comm_barrier(x, seq + 1);     // every rank's slab is final and last call's staging is drained
 
   const int blocks_per_ring = x.blocks / num_rings;
   const int ring = min(x.block / blocks_per_ring, num_rings - 1);
   const int bir = x.block - ring * blocks_per_ring;
   const int dir = (ring == 0) ? 1 : -1;
-  const int prev = (r - dir + W) % W;
+  const int next = ((r + dir) % W + W) % W;
   const long long reg_lo = n4 * ring / num_rings, reg_hi = n4 * (ring + 1) / num_rings;
   const long long chunk4 = (reg_hi - reg_lo + W - 1) / W;
 
   float4* const gr = reinterpret_cast<float4*>(e.grads[r]);
-  const float4* const gp = reinterpret_cast<const float4*>(e.grads[prev]);
   float4* const pr = reinterpret_cast<float4*>(e.params[r]);
-  const float4* const pp = reinterpret_cast<const float4*>(e.params[prev]);
+  const float4* const rv = reinterpret_cast<const float4*>(e.recv[r]);
+  float4* const nrecv = reinterpret_cast<float4*>(e.recv[next]);
+  float4* const nfinal = reinterpret_cast<float4*>(update ? e.params[next] : e.grads[next]);
+  float4* const my_final = update ? pr : gr;
   float4* const my_m = reinterpret_cast<float4*>(e.m);
   float4* const my_v = reinterpret_cast<float4*>(e.v);
   __nv_bfloat16* const sh = reinterpret_cast<__nv_bfloat16*>(e.shadow);
-  unsigned int* const my_flags = x.sig[r] + kBarWords;
-  const unsigned int* const prev_flags = x.sig[prev] + kBarWords;
-  const int nsteps = 2 * (W - 1);
+  const unsigned int* const my_flags = x.sig[r] + kBarWords;
+  unsigned int* const next_flags = x.sig[next] + kBarWords;
+  const float wr = e.weight[r];
+  const int nmsg = 2 * (W - 1);
   bool alive = true;
 
-  for (int step = 0; step < nsteps && W > 1; ++step) {
-    const bool rs = step < W - 1;
-    const int s = rs ? step : step - (W - 1);
-    // chunk handled at this step
-    int cidx = rs ? (r - dir * (1 + s)) : (r - dir * s);
+  for (int k = 0; k <= nmsg && W > 1; ++k) {
+    // chunk handled by message k
+    int cidx = (k <= W - 1) ? (r - dir * k) : (r - dir * (k - W));
     cidx = ((cidx % W) + W) % W;
     const long long c_lo = min(reg_lo + (long long)cidx * chunk4, reg_hi), c_hi = min(c_lo + chunk4, reg_hi);
-    const bool last_rs = rs && (s == W - 2);
     for (int j = bir; j < J; j += blocks_per_ring) {
       const long long lo = min(c_lo + (long long)j * sub4, c_hi), hi = min(lo + sub4, c_hi);
       const int fidx = (ring * J + j) * 16;
-      if (step > 0) {
-        if (threadIdx.x == 0 && alive) alive = spin_until(x, prev_flags + fidx + (step - 1), seq + 2);
+      if (k > 0) {
+        if (threadIdx.x == 0 && alive) alive = spin_until(x, my_flags + fidx + (k - 1), seq + 2);
         __syncthreads();
       }
-      // 4 independent 16-byte peer loads in flight per thread (NVLink latency ~2.5 us: a single
-      // outstanding load per thread caps a CTA at a few GB/s)
       constexpr int U = 4;
       for (long long base = lo + threadIdx.x; base < hi; base += (long long)U * kCommThreads) {
-        float4 in[U], own[U];
+        float4 a[U], g[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const long long i = base + (long long)u * kCommThreads;
-          if (i < hi) in[u] = ld_sys_f4((rs || !update ? gp : pp) + i);
-        }
-        if (rs) {
-#pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const long long i = base + (long long)u * kCommThreads;
-            if (i < hi) own[u] = gr[i];
+          if (i >= hi) continue;
+          if (k >= W) a[u] = my_final[i];                  // finished chunk that prev stored here
+          else {
+            g[u] = gr[i];
+            if (k > 0) a[u] = rv[i];                       // partial sum that prev stored here
           }
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const long long i = base + (long long)u * kCommThreads;
           if (i >= hi) continue;
-          if (rs) {
-            float4 v = in[u];
-            if (s == 0) v = f4_scale(v, e.weight[prev]);
-            float4 acc = f4_fma(own[u], e.weight[r], v);
-            if (last_rs && update) {
+          if (k < W - 1) {                                  // reduce-scatter hop
+            const float4 acc = (k == 0) ? f4_scale(g[u], wr) : f4_fma(g[u], wr, a[u]);
+            st_sys_f4(nrecv + i, acc);
+          } else if (k == W - 1) {                          // owner: finish, fused tail, first all-gather hop
+            float4 acc = f4_fma(g[u], wr, a[u]);
+            if (update) {
               float4 p0 = pr[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
               optim_update4(p0, acc, m0, v0, e.opt);
-              pr[i] = p0; my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
-              if (cast) store_bf16x4(sh + 4 * i, p0);
-            } else {
-              gr[i] = acc;
-              if (last_rs && cast) store_bf16x4(sh + 4 * i, acc);
+              my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
+              acc = p0;
             }
-          } else {
-            if (update) pr[i] = in[u]; else gr[i] = in[u];
-            if (cast) store_bf16x4(sh + 4 * i, in[u]);
+            my_final[i] = acc;
+            if (cast) store_bf16x4(sh + 4 * i, acc);
+            st_sys_f4(nfinal + i, acc);
+          } else {                                          // all-gather hop (k == nmsg: last arrival, no send)
+            if (cast) store_bf16x4(sh + 4 * i, a[u]);
+            if (k < nmsg) st_sys_f4(nfinal + i, a[u]);
           }
         }
       }
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        __threadfence_system();
-        st_release_sys(my_flags + fidx + step, seq + 2);
+      if (k < nmsg) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          __threadfence_system();
+          st_release_sys(next_flags + fidx + k, seq + 2);
+        }
       }
     }
   }
@@ -294,7 +303,7 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
       if (cast) store_bf16x4(sh + 4 * i, val);
     }
   }
-  comm_barrier(x, seq + 3);   // nobody is still pulling from a slab that is about to be reused
+  comm_barrier(x, seq + 3);   // nobody is still storing into a slab that is about to be reused
 }
 
 // ================================================================== compat gossip (1- or 2-hop pull)
@@ -425,10 +434,13 @@ extern "C" int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int n
   LDNN_ARG(num_rings == 1 || num_rings == 2, "ring: num_rings=%d", num_rings);
   LDNN_ARG(!(x->mode & LDNN_X_SELFMIX), "ring: self-weighted mixing is only available on the all-reduce schedule");
   LDNN_ARG(c->blocks >= num_rings, "ring: need >= %d blocks", num_rings);
+  LDNN_ARG(c->world == 1 || x->recv[c->emulate ? 0 : c->rank] != nullptr, "ring: needs the symmetric `recv` staging slab");
   const long long n4 = x->n / 4;
   const long long chunk4 = (n4 / num_rings + c->world) / c->world + 1;
-  // sub-chunks: aim for 128 KB, cap the flag table
-  long long sub4 = 8192;
+  // sub-chunks: every hand-off costs a system fence + a flag round trip, so large payloads use
+  // ~2 sub-chunks per CTA per step (>= 128 KB each); the flag table caps J
+  const int bpr = std::max(1, c->blocks / num_rings);
+  long long sub4 = std::max<long long>(8192, (chunk4 + 2 * bpr - 1) / (2 * bpr));
   int J = (int)((chunk4 + sub4 - 1) / sub4);
   const int maxJ = kFlagWords / (16 * 2);
   if (J > maxJ) { J = maxJ; sub4 = (chunk4 + J - 1) / J; }

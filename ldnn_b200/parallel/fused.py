@@ -89,9 +89,10 @@ class FusedExchanger:
     # ------------------------------------------------------------------ plumbing
     def _recv_buf(self) -> SymmetricBuffer:
         if self._recv is None:
-            t, h, p = K.symm_alloc(self.n * 4, self.rt.device)
+            cap = int(self.engine.flat.total)            # sized for the whole slab, whatever bucket asks first
+            t, h, p = K.symm_alloc(cap * 4, self.rt.device)
             self._recv_t = t
-            self._recv = SymmetricBuffer("recv", p, h, self.n * 4, self.rt)
+            self._recv = SymmetricBuffer("recv", p, h, cap * 4, self.rt)
             if self.world > 1:
                 dist.barrier()
         return self._recv
@@ -130,7 +131,8 @@ class FusedExchanger:
         e.self_coef = a
         if a != 0.0:
             mode |= L.X_SELFMIX
-            rtab = self._recv_buf().table()
+        if a != 0.0 or (self.spec.topology != "allreduce" and self.world > 1):
+            rtab = self._recv_buf().table()          # staging slab: self-mix sums / ring partial sums
             for i in range(self.world):
                 e.recv[i] = rtab[i] + 4 * lo
         e.mode = mode

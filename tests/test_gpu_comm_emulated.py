@@ -57,8 +57,10 @@ def test_reduce_matches_oracle(world, topology):
         sp = ExchangeSpec(topology, "allreduce", agg, 0.5, [float(i + 1) for i in range(world)], world)
         e = L.Exchange()
         tab = emu.table(x)
+        recv = [torch.zeros(n).cuda() for _ in range(world)]
+        rtab = emu.table(recv)
         for i in range(L.MAX_RANKS):
-            e.grads[i] = tab[i]
+            e.grads[i], e.recv[i] = tab[i], rtab[i]
         e.n, e.mode = n, 0
         _, b = reduce_form(sp, 0)
         for i in range(world):
@@ -91,6 +93,7 @@ def test_fused_update_tail(world, topology, kind):
     shadows = [torch.zeros(n, dtype=torch.bfloat16).cuda() for _ in range(world)]
     ref = FlatState([Slot("w", (n,), 0, n)], n, "cuda", opt)
     ref.params.copy_(p0)
+    recv = [torch.zeros(n).cuda() for _ in range(world)]
     for step in range(1, 4):
         grads = _data(world, n, seed=step)
         gmean = torch.stack(grads).double().mean(0).float()
@@ -98,9 +101,9 @@ def test_fused_update_tail(world, topology, kind):
         # emulate mode shares one m/v/shadow pointer per launch: the kernel indexes only the
         # owned slice of m/v, so a single shared m/v is exactly the sharded optimizer state.
         e = L.Exchange()
-        gt, pt = emu.table(grads), emu.table(params)
+        gt, pt, rt_ = emu.table(grads), emu.table(params), emu.table(recv)
         for i in range(L.MAX_RANKS):
-            e.grads[i], e.params[i] = gt[i], pt[i]
+            e.grads[i], e.params[i], e.recv[i] = gt[i], pt[i], rt_[i]
         e.m, e.v, e.shadow = ms[0].data_ptr(), vs[0].data_ptr(), 0
         e.n, e.mode = n, L.X_UPDATE
         for i in range(world):
