@@ -348,6 +348,14 @@ extern "C" int ldnn_conv_query(const ldnn_conv_desc* d, size_t* scratch_bytes, s
   return LDNN_OK;
 }
 
+extern "C" int ldnn_conv_query_grid(const ldnn_conv_desc* d, int* gx, int* gy, int* gz) {
+  Plan pl;
+  int rc = build(*d, pl, true);
+  if (rc) return rc;
+  *gx = (int)pl.launches[0].grid.x; *gy = (int)pl.launches[0].grid.y; *gz = (int)pl.launches[0].grid.z;
+  return LDNN_OK;
+}
+
 extern "C" int ldnn_conv_plan_create(const ldnn_conv_desc* d, void** plan) {
   Plan* pl = new Plan();
   int rc = build(*d, *pl, false);

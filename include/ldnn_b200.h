@@ -48,6 +48,8 @@ typedef struct {
  * tap — fewer than stride^2 means part of dx is not written and the caller must pre-zero + accumulate */
 int ldnn_conv_query(const ldnn_conv_desc* d, size_t* scratch_bytes, size_t* ticket_count, int* launches,
                     int* covered_classes);
+/* launch grid the plan would use (for autotuners) */
+int ldnn_conv_query_grid(const ldnn_conv_desc* d, int* gx, int* gy, int* gz);
 int ldnn_conv_plan_create(const ldnn_conv_desc* d, void** plan);
 int ldnn_conv_plan_run(void* plan, void* stream);
 void ldnn_conv_plan_destroy(void* plan);

@@ -68,6 +68,7 @@ class NativeEngine(Engine):
         # while backward continues.  Off in deterministic mode (shared split-K scratch).
         self.concurrent = not self.deterministic and not os.environ.get("LDNN_SERIAL")
         self._opt_stream = None
+        self.autotune = not os.environ.get("LDNN_NO_AUTOTUNE")
         self.graph_kernel_launches = 0    # kernels launched through CUDA-graph replays (the library's
                                           # own counter only sees eager launches)
         torch.cuda.set_device(self.device)
@@ -333,7 +334,18 @@ class _StepPlan:
                     descs.append((K.DGRAD, geo))
         ws = K.Workspace(dev)
         atomic = not eng.deterministic
-        ws.reserve(max(K.conv_query(m, *g, atomic_out=(atomic and m == K.WGRAD))[0] for m, g in descs))
+        need = 0
+        for m, g in descs:
+            need = max(need, K.conv_query(m, *g, atomic_out=(atomic and m == K.WGRAD))[0])
+            if eng.autotune:                        # the tuner may pick any candidate: size for the largest
+                n_total = g[4] if m == K.FPROP else g[3]
+                for bn, sp in K.conv_candidates(m, g, n_total):
+                    try:
+                        need = max(need, K.conv_query(m, *g, block_n=bn, splits=sp,
+                                                      atomic_out=(atomic and m == K.WGRAD))[0])
+                    except L.LdnnError:
+                        pass
+        ws.reserve(min(need, 1 << 30))
         self.ws = ws
         partial_max = 0
         for u in spec.conv_units():
@@ -433,11 +445,12 @@ class _StepPlan:
         fast = not eng.deterministic
         fsum = eng.bn_sums[2 * o:2 * o + 2 * Cc] if (fast and self.training) else None
         if ci.im2col:
-            plan = K.ConvPlan(K.FPROP, n, ci.P, ci.Q, ci.kdim, u.cout, 1, 1, 0, self.col[u.conv_key], w, yraw,
-                              workspace=self.ws, bn_sums=fsum)
+            geo, xin = (n, ci.P, ci.Q, ci.kdim, u.cout, 1, 1, 0), self.col[u.conv_key]
         else:
-            plan = K.ConvPlan(K.FPROP, n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad, self.act[u.src], w, yraw,
-                              workspace=self.ws, bn_sums=fsum)
+            geo, xin = (n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad), self.act[u.src]
+        bn_, sp_ = K.tuned_conv_config(K.FPROP, geo, lambda b, s_: K.ConvPlan(K.FPROP, *geo, xin, w, yraw, bn_sums=fsum,
+                                                                          block_n=b, splits=s_), eng.autotune)
+        plan = K.ConvPlan(K.FPROP, *geo, xin, w, yraw, workspace=self.ws, bn_sums=fsum, block_n=bn_, splits=sp_)
         self._add(plan.run, plan.num_launches)
         if fast:
             self._add(lambda: K.bn_fwd_apply_sums(yraw, fsum, gamma, beta, rm, rv, nbt, sm, si, res, out, M, Cc, u.relu,
@@ -487,8 +500,12 @@ class _StepPlan:
             geo = (n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad)
             xin = self.act[u.src]
         atomic = not eng.deterministic
-        wg = K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, workspace=self.ws, atomic_out=atomic)
-        if atomic and K.conv_query(K.WGRAD, *geo)[0] > 0:        # split-K → red.add into a zeroed slice
+        bn_, sp_ = K.tuned_conv_config(K.WGRAD, geo, lambda b, s_: K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw,
+                                                                          atomic_out=atomic, block_n=b, splits=s_),
+                                       eng.autotune and atomic)
+        wg = K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, workspace=self.ws, atomic_out=atomic, block_n=bn_,
+                        splits=sp_)
+        if atomic and K.conv_query(K.WGRAD, *geo, block_n=bn_, splits=sp_)[0] > 0:   # split-K → red.add into a zeroed slice
             sl = eng.flat.by_key[u.conv_key + ".weight"]
             self.zero_ranges.append((sl.offset, sl.offset + sl.numel))
         self._add(wg.run, wg.num_launches, side=True)
@@ -501,7 +518,11 @@ class _StepPlan:
         if not acc and not full_cover:
             self._add(lambda: dx.zero_(), 0)
             acc = True
-        dg = K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx if acc else None, accumulate=acc, workspace=self.ws)
+        bn_, sp_ = K.tuned_conv_config(K.DGRAD, geo, lambda b, s_: K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx,
+                                                                          accumulate=True, block_n=b, splits=s_),
+                                       eng.autotune)
+        dg = K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx if acc else None, accumulate=acc, workspace=self.ws,
+                        block_n=bn_, splits=sp_)
         self._add(dg.run, dg.num_launches)
         written.add(u.src)
 

@@ -38,6 +38,9 @@ class ConvPlan:
         sb, tk, nl, cc = C.c_size_t(0), C.c_size_t(0), C.c_int(0), C.c_int(0)
         L.check(L.lib().ldnn_conv_query(C.byref(d), C.byref(sb), C.byref(tk), C.byref(nl), C.byref(cc)))
         self.scratch_bytes, self.ticket_count, self.num_launches = sb.value, tk.value, nl.value
+        gx, gy, gz = C.c_int(0), C.c_int(0), C.c_int(0)
+        L.lib().ldnn_conv_query_grid(C.byref(d), C.byref(gx), C.byref(gy), C.byref(gz))
+        self.grid = (gx.value, gy.value, gz.value)
         self._keep = [x, w, y, dw, addend, bn_sums]
         if sb.value:
             if workspace is not None:
@@ -59,6 +62,66 @@ class ConvPlan:
                 L.lib().ldnn_conv_plan_destroy(self._plan)
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------------------------------------
+# per-shape autotuning of (block_n, splits): these layers are latency/fill-rate bound, so the best
+# tiling depends on how many CTAs it yields — measured once per shape at plan-build time.
+_TUNE_CACHE = {}
+
+
+def _time_plan(plan, iters=10, reps=3):
+    best = float("inf")
+    for _ in range(2):
+        plan.run()
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(iters):
+            plan.run()
+        b.record()
+        torch.cuda.synchronize()
+        best = min(best, a.elapsed_time(b) / iters)
+    return best
+
+
+def conv_candidates(mode, geo, n_total):
+    N, H, W, Cin, Cout, R, stride, pad = geo
+    bns = [b for b in (64, 128, 256) if n_total % b == 0 and (b < 256 or mode == WGRAD)]
+    out = []
+    for bn in bns:
+        for sp in (1, 2, 3, 4, 6, 8, 9, 12, 16, 24, 32):
+            out.append((bn, sp))
+    return out
+
+
+def tuned_conv_config(mode, geo, make_plan, enabled=True):
+    """Returns (block_n, splits) — (0, 0) = library heuristics.  `make_plan(block_n, splits)` must
+    build a runnable plan (private scratch) for timing."""
+    if not enabled:
+        return 0, 0
+    key = (mode,) + tuple(geo)
+    if key in _TUNE_CACHE:
+        return _TUNE_CACHE[key]
+    N, H, W, Cin, Cout, R, stride, pad = geo
+    n_total = Cout if mode == FPROP else Cin
+    best_cfg, best_t = (0, 0), _time_plan(make_plan(0, 0))
+    seen = set()
+    for bn, sp in conv_candidates(mode, geo, n_total):
+        try:
+            plan = make_plan(bn, sp)
+        except L.LdnnError:
+            continue
+        sig = (bn, plan.grid)
+        if sig in seen or not (24 <= plan.grid[0] * plan.grid[1] * plan.grid[2] <= 1200):
+            continue
+        seen.add(sig)
+        t = _time_plan(plan)
+        if t < best_t * 0.97:                      # only leave the heuristic for a clear win
+            best_cfg, best_t = (bn, sp), t
+    _TUNE_CACHE[key] = best_cfg
+    return best_cfg
 
 
 class Workspace:
