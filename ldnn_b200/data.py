@@ -90,7 +90,7 @@ def make_synthetic(n_train=4096, n_val=1024, n_test=1024, num_classes=10, hw=32,
     def draw(n, s):
         gg = torch.Generator().manual_seed(seed * 1000 + s)
         y = torch.randint(0, num_classes, (n,), generator=gg)
-        x = 0.75 * protos[y] + torch.randn(n, channels, hw, hw, generator=gg)
+        x = 0.25 * protos[y] + torch.randn(n, channels, hw, hw, generator=gg)      # SNR low enough that curves bend
         return ArrayDataset(x.contiguous(), y.numpy())
 
     return DataBundle(draw(n_train, 1), draw(n_val, 2), draw(n_test, 3), num_classes, "synthetic")
