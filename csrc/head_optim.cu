@@ -110,11 +110,17 @@ head_reduce_kernel(const float* __restrict__ pooled, const float* __restrict__ d
         float acc[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-        for (int n = 0; n < N; ++n) {
-          const float pv = pooled[(size_t)n * C + c];
+        for (int n0 = 0; n0 < N; n0 += 8) {                 // 8 independent loads in flight per thread
+          float pv[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (j0 + j < classes) acc[j] += s_dl[n * classes + j0 + j] * pv;
+          for (int u = 0; u < 8; ++u) pv[u] = (n0 + u < N) ? pooled[(size_t)(n0 + u) * C + c] : 0.f;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            if (n0 + u >= N) break;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (j0 + j < classes) acc[j] += s_dl[(n0 + u) * classes + j0 + j] * pv[u];
+          }
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j)

@@ -5,8 +5,8 @@ lines = [l for l in open(path) if l.startswith('"')]
 r = csv.reader(lines); hdr = next(r)
 ik, iv, ig = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size")
 rows = [(row[ik], float(row[iv].replace(",", "")), row[ig]) for row in r]
-idx = [i for i, (k, _, _) in enumerate(rows) if "optim_kernel" in k]
-step = rows[idx[-2] + 1: idx[-1] + 1]
+idx = [i for i, (k, _, _) in enumerate(rows) if "im2col_stem" in k]      # first kernel of every step
+step = rows[idx[-2]: idx[-1]]
 tot = sum(v for _, v, _ in step)
 print(f"kernels in step {len(step)}  total {tot / 1e3:.1f} us (ncu, serialised, cold caches)")
 agg = collections.defaultdict(lambda: [0, 0.0])

@@ -1,6 +1,7 @@
 """A few eager (no CUDA graph) training steps of the flagship model, for ncu launch lists / captures."""
 import os, sys
 os.environ["LDNN_NO_GRAPH"] = "1"
+os.environ.setdefault("LDNN_NO_AUTOTUNE", "1")   # event timing under ncu would mis-tune
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from ldnn_b200.engine import OptimConfig
