@@ -88,6 +88,7 @@ struct Plan {
   float* scratch;
   unsigned int* tickets;
   float* stats;
+  BnBwdFuse fuse;
 };
 
 static void pixel_box(int Wd, int Hd, int Nd, int target, ConvParams& p, ConvClass& c) {
@@ -141,6 +142,14 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   plan.addend = d.addend ? d.addend : plan.out;
   plan.scratch = d.scratch; plan.tickets = d.tickets;
   plan.stats = (d.mode == MODE_FPROP) ? d.bn_sums : nullptr;
+  memset(&plan.fuse, 0, sizeof(plan.fuse));
+  if (d.mode == MODE_DGRAD && d.fuse_sums) {
+    LDNN_ARG(d.fuse_out && d.fuse_y && d.fuse_mean && d.fuse_invstd, "dgrad BN-backward fusion needs out/y/mean/invstd");
+    plan.fuse.out = reinterpret_cast<const __nv_bfloat16*>(d.fuse_out);
+    plan.fuse.y = reinterpret_cast<const __nv_bfloat16*>(d.fuse_y);
+    plan.fuse.mean = d.fuse_mean; plan.fuse.invstd = d.fuse_invstd; plan.fuse.sums = d.fuse_sums;
+    plan.fuse.relu = d.fuse_relu;
+  }
 
   const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(d.x);
   const __nv_bfloat16* yb = reinterpret_cast<const __nv_bfloat16*>(d.y);
@@ -314,7 +323,7 @@ static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
   }
   LDNN_CUDA(launch_pdl(conv_gemm_kernel<MODE, BN>, L.grid, dim3(Cfg::kThreads), (size_t)Cfg::kSmemBytes, st, L.maps, L.p,
                        pl.out, pl.addend, pl.scratch ? pl.scratch + L.scratch_off : nullptr,
-                       pl.tickets ? pl.tickets + L.ticket_off : nullptr, pl.stats));
+                       pl.tickets ? pl.tickets + L.ticket_off : nullptr, pl.stats, pl.fuse));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return LDNN_OK;
 }

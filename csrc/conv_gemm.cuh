@@ -62,6 +62,18 @@ struct ConvParams {
   ConvClass cls[4];
 };
 
+// dgrad only: the BN-backward reduction of the layer that OWNS dx (dy = dx * (out > 0);
+// sums += (sum dy, sum dy * xhat)) is folded into this epilogue when this dgrad is the last
+// contribution to dx — one launch fewer per layer and dx is not re-read.
+struct BnBwdFuse {
+  const __nv_bfloat16* out;    // post-activation output of the owning layer (ReLU mask), same shape as dx
+  const __nv_bfloat16* y;      // its pre-BN conv output
+  const float* mean;
+  const float* invstd;
+  float* sums;                 // [2][C]
+  int relu;
+};
+
 struct ConvMaps {
   CUtensorMap act[4];   // shifted operand (x for fprop/wgrad, dy for dgrad), one per parity view
   CUtensorMap other;    // weights (fprop/dgrad, 2-D) or dy (wgrad, 4-D)
@@ -81,7 +93,7 @@ template <int MODE, int BLOCK_N>
 __global__ void __launch_bounds__(192, 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void* __restrict__ out,
                  const void* __restrict__ addend, float* __restrict__ scratch, unsigned int* __restrict__ tickets,
-                 float* __restrict__ stats) {
+                 float* __restrict__ stats, const BnBwdFuse fuse) {
   using Cfg = ConvCfg<BLOCK_N>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -220,7 +232,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
       row_off = kc.out_base + n * p.sN + h * p.sH + w * p.sW;
     }
 
-    auto emit = [&](int col0, const float (&v)[32]) {
+    auto emit = [&](int col0, float (&v)[32]) {
       if (!row_ok) return;
       if (MODE == MODE_WGRAD) {
         float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + row_off + n0 + col0);
@@ -256,6 +268,13 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
 #pragma unroll
           for (int j = 0; j < 4; ++j) ob[j] = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
           *reinterpret_cast<uint4*>(o + 8 * i) = ov;
+          if (MODE == MODE_DGRAD) {            // hand the stored (rounded) values back for the fused BN reduce
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 t = __bfloat1622float2(ob[j]);
+              v[8 * i + 2 * j] = t.x; v[8 * i + 2 * j + 1] = t.y;
+            }
+          }
         }
       }
     };
@@ -266,10 +285,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     // pipeline smem and 2*BLOCK_N red.add's per CTA accumulate into stats[2][Cout].
     float* red = reinterpret_cast<float*>(smem);          // [BLOCK_N/32][4][2][32]
     const bool do_stats = (MODE == MODE_FPROP) && (stats != nullptr);
-    auto col_stats = [&](int col0, const float (&v)[32]) {
-      float a[32], b[32];
-#pragma unroll
-      for (int i = 0; i < 32; ++i) { a[i] = row_ok ? v[i] : 0.f; b[i] = a[i] * a[i]; }
+    const bool do_bwd = (MODE == MODE_DGRAD) && (fuse.sums != nullptr);
+    float* const sum_dst = do_bwd ? fuse.sums : stats;
+    auto col_reduce = [&](int col0, float (&a)[32], float (&b)[32]) {
       const uint32_t lane = lane_id();
 #pragma unroll
       for (int off = 16; off >= 1; off >>= 1) {
@@ -286,13 +304,41 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
       dst[lane] = a[0];
       dst[32 + lane] = b[0];
     };
+    auto col_stats = [&](int col0, const float (&v)[32]) {
+      float a[32], b[32];
+      if (MODE == MODE_DGRAD) {
+        // dy = dx * (out > 0);  b = dy * xhat
+        const __nv_bfloat16* op = fuse.out + row_off + n0 + col0;
+        const __nv_bfloat16* yp = fuse.y + row_off + n0 + col0;
+#pragma unroll
+        for (int i8 = 0; i8 < 4; ++i8) {
+          float o8[8], y8[8];
+          if (row_ok) {
+            bf16x8_to_float(*reinterpret_cast<const uint4*>(yp + 8 * i8), y8);
+            if (fuse.relu) bf16x8_to_float(*reinterpret_cast<const uint4*>(op + 8 * i8), o8);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int i = 8 * i8 + j;
+            float g = row_ok ? v[i] : 0.f;
+            if (row_ok && fuse.relu && !(o8[j] > 0.f)) g = 0.f;
+            const float xh = row_ok ? (y8[j] - __ldg(fuse.mean + n0 + col0 + i)) * __ldg(fuse.invstd + n0 + col0 + i) : 0.f;
+            a[i] = g; b[i] = g * xh;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) { a[i] = row_ok ? v[i] : 0.f; b[i] = a[i] * a[i]; }
+      }
+      col_reduce(col0, a, b);
+    };
     auto flush_stats = [&]() {
       asm volatile("bar.sync 2, 128;" ::: "memory");
       for (int idx = et; idx < 2 * BLOCK_N; idx += 128) {
         const int which = idx / BLOCK_N, col = idx % BLOCK_N;
         const float* src = red + (col >> 5) * 4 * 64 + which * 32 + (col & 31);
         const float t = src[0] + src[64] + src[128] + src[192];
-        atomicAdd(&stats[(size_t)which * p.n_total + n0 + col], t);
+        atomicAdd(&sum_dst[(size_t)which * p.n_total + n0 + col], t);
       }
     };
 
@@ -307,9 +353,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
         emit(c, v);
-        if (do_stats) col_stats(c, v);
+        if (do_stats || do_bwd) col_stats(c, v);
       }
-      if (do_stats) flush_stats();
+      if (do_stats || do_bwd) flush_stats();
     } else {
       // ---- split-K: park the partial tile, take a ticket, last arriver reduces ----
       const int tiles_n = gridDim.y;
@@ -370,9 +416,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
             }
           }
           emit(c, v);
-          if (do_stats) col_stats(c, v);
+          if (do_stats || do_bwd) col_stats(c, v);
         }
-        if (do_stats) flush_stats();
+        if (do_stats || do_bwd) flush_stats();
         if (et == 0) tickets[tile_lin] = 0;   // ready for the next launch
       }
     }

@@ -42,6 +42,11 @@ typedef struct {
                           once per step) instead of going through scratch + ticket; not bit-reproducible */
   float* bn_sums;      /* fprop, optional: fp32 [2][Cout]; the epilogue ADDS per-channel sum and sum of
                           squares of the output (fused BN statistics); caller zeroes it per step        */
+  /* dgrad, optional: fold the BN-backward reduction of the layer that owns dx into the epilogue
+   * (valid only when this dgrad is the LAST contribution to dx): fuse_sums[2][Cin] += (sum dy, sum dy*xhat),
+   * dy = dx * (fuse_out > 0 if fuse_relu).  fuse_out / fuse_y are bf16 tensors shaped like dx. */
+  const void* fuse_out; const void* fuse_y; const float* fuse_mean; const float* fuse_invstd; float* fuse_sums;
+  int fuse_relu;
 } ldnn_conv_desc;
 
 /* sizes a plan needs; covered_classes (dgrad): how many of the stride^2 output parity classes receive any

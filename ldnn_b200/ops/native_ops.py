@@ -24,7 +24,7 @@ class ConvPlan:
                  x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, dw: Optional[torch.Tensor] = None,
                  addend: Optional[torch.Tensor] = None, accumulate: bool = False, block_n: int = 0, splits: int = 0,
                  workspace=None, desc_override=None, bn_sums: Optional[torch.Tensor] = None,
-                 atomic_out: bool = False):
+                 atomic_out: bool = False, bn_bwd_fuse=None):
         d = L.ConvDesc()
         d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
         d.block_n, d.splits, d.accumulate = block_n, splits, int(accumulate)
@@ -33,6 +33,11 @@ class ConvPlan:
         d.addend = 0 if addend is None else addend.data_ptr()
         d.bn_sums = 0 if bn_sums is None else bn_sums.data_ptr()
         d.atomic_out = int(atomic_out)
+        if bn_bwd_fuse is not None:        # (out, y, mean, invstd, sums, relu) of the layer that owns dx
+            f_out, f_y, f_mean, f_is, f_sums, f_relu = bn_bwd_fuse
+            d.fuse_out, d.fuse_y, d.fuse_mean = f_out.data_ptr(), f_y.data_ptr(), f_mean.data_ptr()
+            d.fuse_invstd, d.fuse_sums, d.fuse_relu = f_is.data_ptr(), f_sums.data_ptr(), int(f_relu)
+            self._fuse_keep = bn_bwd_fuse
         if desc_override:
             d.a_lbo, d.a_sbo, d.b_lbo, d.b_sbo = desc_override
         sb, tk, nl, cc = C.c_size_t(0), C.c_size_t(0), C.c_int(0), C.c_int(0)

@@ -94,3 +94,29 @@ def test_split_k_is_deterministic_and_reusable():
     for _ in range(3):
         y.zero_(); plan.run(); torch.cuda.synchronize()
         assert torch.equal(y, y0)
+
+
+@pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (6, 8, 8, 256, 512, 3, 2, 1), (64, 2, 2, 1024, 1024, 3, 1, 1)])
+@pytest.mark.parametrize("relu", [True, False])
+def test_dgrad_fused_bn_backward_reduce(case, relu):
+    """dgrad epilogue also accumulates (sum dy, sum dy*xhat) of the layer that owns dx."""
+    from gpu_util import make_conv_case
+    from ldnn_b200.ops import native_ops as K
+    N, H, W, Cin, Cout, R, s, p = case
+    x, w, dy, P, Q = make_conv_case(*case)
+    g = torch.Generator().manual_seed(11)
+    out = torch.randn(N, H, W, Cin, generator=g).cuda().bfloat16()          # owner's post-activation output
+    y = torch.randn(N, H, W, Cin, generator=g).cuda().bfloat16()            # owner's pre-BN output
+    mean, invstd = torch.randn(Cin, generator=g).cuda() * 0.1, (torch.rand(Cin, generator=g) + 0.5).cuda()
+    sums = torch.zeros(2 * Cin, device="cuda")
+    dx = torch.zeros(N, H, W, Cin, device="cuda", dtype=torch.bfloat16)
+    K.ConvPlan(K.DGRAD, N, H, W, Cin, Cout, R, s, p, dx, w.view(Cout, -1), dy, addend=dx, accumulate=True,
+               bn_bwd_fuse=(out, y, mean, invstd, sums, relu)).run()
+    torch.cuda.synchronize()
+    d = dx.float().view(-1, Cin)
+    if relu:
+        d = d * (out.float().view(-1, Cin) > 0)
+    xh = (y.float().view(-1, Cin) - mean) * invstd
+    want_a, want_b = d.sum(0), (d * xh).sum(0)
+    assert torch.allclose(sums[:Cin], want_a, rtol=2e-3, atol=2e-3 * float(want_a.abs().max()))
+    assert torch.allclose(sums[Cin:], want_b, rtol=2e-3, atol=2e-3 * float(want_b.abs().max()))
