@@ -86,11 +86,12 @@ struct ConvCfg {
   static constexpr int kBBytes = BLOCK_N * 64 * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-  static constexpr int kThreads = 192;
+  static constexpr int kEpiWarps = 8;          // two warps per TMEM lane quarter, each takes half of the columns
+  static constexpr int kThreads = 64 + 32 * kEpiWarps;
 };
 
 template <int MODE, int BLOCK_N>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(64 + 32 * 8, 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void* __restrict__ out,
                  const void* __restrict__ addend, float* __restrict__ scratch, unsigned int* __restrict__ tickets,
                  float* __restrict__ stats, const BnBwdFuse fuse) {
@@ -213,7 +214,10 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     // ===================== epilogue (warps 2..5) =====================
     const int q = warp & 3;                    // TMEM lane quarter this warp may access
     const int row = q * 32 + lane_id();        // accumulator row == M index inside the tile
-    const int et = (warp - 2) * 32 + lane_id();  // 0..127 epilogue thread id
+    const int et = (warp - 2) * 32 + lane_id();  // 0..255 epilogue thread id
+    const int chalf = (warp - 2) >> 2;           // which half of the tile's columns this warp drains
+    constexpr int kColsPerWarp = BLOCK_N / 2;
+    const int c_begin = chalf * kColsPerWarp, c_end = c_begin + kColsPerWarp;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
 
@@ -300,7 +304,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
           b[i] = keep_b + __shfl_xor_sync(0xffffffffu, send_b, off);
         }
       }
-      float* dst = red + ((col0 >> 5) * 4 + (warp - 2)) * 64;
+      float* dst = red + ((col0 >> 5) * 4 + q) * 64;
       dst[lane] = a[0];
       dst[32 + lane] = b[0];
     };
@@ -333,8 +337,8 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
       col_reduce(col0, a, b);
     };
     auto flush_stats = [&]() {
-      asm volatile("bar.sync 2, 128;" ::: "memory");
-      for (int idx = et; idx < 2 * BLOCK_N; idx += 128) {
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      for (int idx = et; idx < 2 * BLOCK_N; idx += 256) {
         const int which = idx / BLOCK_N, col = idx % BLOCK_N;
         const float* src = red + (col >> 5) * 4 * 64 + which * 32 + (col & 31);
         const float t = src[0] + src[64] + src[128] + src[192];
@@ -345,7 +349,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
     if (kc.splits == 1 || (MODE == MODE_WGRAD && p.atomic_out)) {
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N; c += 32) {
+      for (int c = c_begin; c < c_end; c += 32) {
         uint32_t r[32];
         tmem_ld_32x32(t_row + c, r);
         tmem_ld_wait();
@@ -365,7 +369,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
       const int stride_splits = (MODE == MODE_WGRAD) ? kc.splits : p.max_splits;
       float4* part = reinterpret_cast<float4*>(scratch) + (tile_lin * stride_splits + split) * (BLOCK_N / 4) * 128;
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N; c += 32) {
+      for (int c = c_begin; c < c_end; c += 32) {
         uint32_t r[32];
         tmem_ld_32x32(t_row + c, r);
         tmem_ld_wait();
@@ -374,7 +378,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
           part[(c / 4 + i) * 128 + row] = make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]),
                                                       __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       if (et == 0) {
         __threadfence();                       // one fence per CTA publishes every epilogue thread's partial
         const unsigned int old = atomicAdd(&tickets[tile_lin], 1u);
@@ -382,11 +386,11 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
         if (last) __threadfence();
         *last_flag = last;
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       if (*last_flag) {
         const float4* base = reinterpret_cast<const float4*>(scratch) + tile_lin * stride_splits * (BLOCK_N / 4) * 128;
 #pragma unroll 1
-        for (int c = 0; c < BLOCK_N; c += 32) {
+        for (int c = c_begin; c < c_end; c += 32) {
           float v[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = 0.f;
