@@ -93,7 +93,7 @@ def _time_plan(plan, iters=10, reps=3):
 
 def conv_candidates(mode, geo, n_total):
     N, H, W, Cin, Cout, R, stride, pad = geo
-    bns = [b for b in (64, 128, 256) if n_total % b == 0 and (b < 256 or mode == WGRAD)]
+    bns = [b for b in (64, 128, 256) if n_total % b == 0]
     out = []
     for bn in bns:
         for sp in (1, 2, 3, 4, 6, 8, 9, 12, 16, 24, 32):
