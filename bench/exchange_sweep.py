@@ -43,7 +43,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max_mb", type=int, default=1024)
     ap.add_argument("--iters", type=int, default=20)
-    ap.add_argument("--blocks", type=int, default=64)
+    ap.add_argument("--blocks", type=int, default=64)   # the sweep has the GPU to itself: 64 CTAs for every kernel
     ap.add_argument("--out", default="gpurun_out/exchange_sweep.json")
     a = ap.parse_args()
     from ldnn_b200.launch import init_runtime, shutdown

@@ -63,6 +63,7 @@ class NativeEngine(Engine):
         # fixed) or the ticketed two-level reduction (bit-reproducible, ~2x more launches).
         self.deterministic = bool(os.environ.get("LDNN_DETERMINISTIC"))
         self.bucket_elems = int(os.environ.get("LDNN_BUCKET_MB", "32")) * (1 << 20) // 4
+        self._bucket_env = "LDNN_BUCKET_MB" in os.environ
         # graph topology: wgrad runs on a side stream concurrently with the dgrad -> bn-backward chain
         # (both only read dy_raw), and the local optimizer runs bucket by bucket on a third stream
         # while backward continues.  Off in deterministic mode (shared split-K scratch).
@@ -237,6 +238,8 @@ class NativeEngine(Engine):
     def train_step_sync(self, x, y, exchanger):
         """Product schedule (--sync step): forward/backward with the fused exchange+update of each
         gradient bucket overlapped with the rest of backward (BASELINE north star)."""
+        if not self._bucket_env and not self._plans and getattr(exchanger.spec, "topology", "allreduce") != "allreduce":
+            self.bucket_elems = 64 * (1 << 20) // 4      # rings are latency-bound per launch: fewer, larger buckets
         p = self._plan(int(x.shape[0]), True)
         exchanger.begin_step(self)
         p.run_bucketed(x, y, lambda lo, hi: exchanger.exchange_bucket(self, lo, hi))

@@ -68,7 +68,9 @@ class FusedExchanger:
             raise L.LdnnError(f"fused exchange supports up to {L.MAX_RANKS} ranks on one NVSwitch domain")
         if not hasattr(engine, "symm_handle"):
             raise L.LdnnError("engine does not keep its flat slabs in symmetric memory")
-        self.blocks = comm_blocks or 64
+        # measured on 4 and 8 B200 (tools/gpu_tune_overlap.sh): the two-shot kernel saturates NVLink with 32
+        # CTAs and leaves more SMs to the overlapped backward; the rings want 64
+        self.blocks = comm_blocks or (32 if spec.topology == "allreduce" else 64)
         self.timeout_cycles = int(watchdog_ms * SM_CLOCK_KHZ)
         self.epoch = 0
         self.launches = 0
