@@ -255,6 +255,8 @@ def make_engine(cfg, rt) -> Engine:
         if not rt.is_cuda:
             raise RuntimeError("--engine native needs a CUDA device (sm_100a)")
         from .models.native import NativeEngine
+        # rings are latency-bound per launch: fewer, larger buckets for the overlapped per-step exchange
+        bucket_mb = 64 if (cfg.sync == "step" and cfg.topology != "allreduce") else 32
         return NativeEngine(spec, rt.device, opt, batch_size=cfg.batch_size, world_size=rt.world_size,
-                            rank=rt.rank)
+                            rank=rt.rank, bucket_mb=bucket_mb)
     return TorchEngine(spec, rt.device, opt)

@@ -54,7 +54,7 @@ class NativeEngine(Engine):
     permuted_layout = True
 
     def __init__(self, spec: NetSpec, device, opt: OptimConfig, batch_size: int = 64, world_size: int = 1,
-                 rank: int = 0, init: bool = True, use_graph: bool = True):
+                 rank: int = 0, init: bool = True, use_graph: bool = True, bucket_mb: Optional[int] = None):
         if not L.available():
             raise L.LdnnError("libldnn_b200.so is not built; run `python -m ldnn_b200.build`")
         self.spec, self.device, self.max_batch = spec, canonical_device(device), batch_size
@@ -63,7 +63,8 @@ class NativeEngine(Engine):
         # fixed) or the ticketed two-level reduction (bit-reproducible, ~2x more launches).
         self.deterministic = bool(os.environ.get("LDNN_DETERMINISTIC"))
         self.bucket_elems = int(os.environ.get("LDNN_BUCKET_MB", "32")) * (1 << 20) // 4
-        self._bucket_env = "LDNN_BUCKET_MB" in os.environ
+        if bucket_mb and "LDNN_BUCKET_MB" not in os.environ:
+            self.bucket_elems = bucket_mb * (1 << 20) // 4
         # graph topology: wgrad runs on a side stream concurrently with the dgrad -> bn-backward chain
         # (both only read dy_raw), and the local optimizer runs bucket by bucket on a third stream
         # while backward continues.  Off in deterministic mode (shared split-K scratch).
@@ -238,8 +239,6 @@ class NativeEngine(Engine):
     def train_step_sync(self, x, y, exchanger):
         """Product schedule (--sync step): forward/backward with the fused exchange+update of each
         gradient bucket overlapped with the rest of backward (BASELINE north star)."""
-        if not self._bucket_env and not self._plans and getattr(exchanger.spec, "topology", "allreduce") != "allreduce":
-            self.bucket_elems = 64 * (1 << 20) // 4      # rings are latency-bound per launch: fewer, larger buckets
         p = self._plan(int(x.shape[0]), True)
         exchanger.begin_step(self)
         p.run_bucketed(x, y, lambda lo, hi: exchanger.exchange_bucket(self, lo, hi))
