@@ -81,7 +81,7 @@ struct Launch {
   int covered_classes = 1;                  // dgrad: parity classes that have taps
 };
 struct Plan {
-  int mode, block_n;
+  int mode, block_n, cluster = 1;
   std::vector<Launch> launches;
   void* out;
   const void* addend;
@@ -138,6 +138,7 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   LDNN_ARG(bn_ == 64 || bn_ == 128 || bn_ == 256, "block_n %d", bn_);
   LDNN_ARG(n_total % bn_ == 0, "N=%d not a multiple of block_n=%d", n_total, bn_);
   plan.mode = d.mode; plan.block_n = bn_;
+  plan.cluster = (d.cluster == 2 && d.mode != MODE_WGRAD && bn_ >= 128) ? 2 : 1;
   plan.out = (d.mode == MODE_FPROP) ? d.y : (d.mode == MODE_DGRAD ? const_cast<void*>(d.x) : d.dw);
   plan.addend = d.addend ? d.addend : plan.out;
   plan.scratch = d.scratch; plan.tickets = d.tickets;
@@ -220,9 +221,10 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
         int rc = x_view_map(&L.maps.act[v], v < nviews ? v / 2 : 0, v < nviews ? v % 2 : 0, box);
         if (rc) return rc;
       }
-      int rc = w_map(&L.maps.other, bn_);
+      int rc = w_map(&L.maps.other, bn_ / plan.cluster);
       if (rc) return rc;
     }
+    if (plan.cluster == 2) LDNN_ARG(m_tiles % 2 == 0, "cluster=2 needs an even number of M tiles (%d)", m_tiles);
   } else if (d.mode == MODE_DGRAD) {
     // one class per output parity (1 class for stride 1), all in one launch
     p.kb_per_tap = d.Cout / 64; p.red_ch = d.Cout;
@@ -260,6 +262,11 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
         p.cls[ncls++] = c;
       }
     LDNN_ARG(ncls >= 1, "dgrad: no taps at all");
+    if (plan.cluster == 2)
+      for (int i = 0; i < ncls; ++i) {
+        const int mt = (i + 1 < ncls ? p.cls[i + 1].m_begin : m_total) - p.cls[i].m_begin;
+        LDNN_ARG(mt % 2 == 0, "cluster=2 needs an even number of M tiles per parity class (%d)", mt);
+      }
     p.num_classes = ncls;
     L.covered_classes = covered;
     p.max_splits = 1;
@@ -312,28 +319,47 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   return LDNN_OK;
 }
 
-template <int MODE, int BN>
+template <int MODE, int BN, int CL>
 static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
   using Cfg = ConvCfg<BN>;
   static bool configured = false;
   if (!configured) {
-    LDNN_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<MODE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    LDNN_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<MODE, BN, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    Cfg::kSmemBytes));
     configured = true;
   }
-  LDNN_CUDA(launch_pdl(conv_gemm_kernel<MODE, BN>, L.grid, dim3(Cfg::kThreads), (size_t)Cfg::kSmemBytes, st, L.maps, L.p,
-                       pl.out, pl.addend, pl.scratch ? pl.scratch + L.scratch_off : nullptr,
-                       pl.tickets ? pl.tickets + L.ticket_off : nullptr, pl.stats, pl.fuse));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = L.grid; cfg.blockDim = dim3(Cfg::kThreads); cfg.dynamicSmemBytes = Cfg::kSmemBytes; cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (CL > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = CL; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  cfg.attrs = attr; cfg.numAttrs = na;
+  LDNN_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<MODE, BN, CL>, L.maps, L.p, pl.out, pl.addend,
+                               pl.scratch ? pl.scratch + L.scratch_off : nullptr,
+                               pl.tickets ? pl.tickets + L.ticket_off : nullptr, pl.stats, pl.fuse));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return LDNN_OK;
 }
 
 template <int MODE>
 static int launch_bn(const Launch& L, const Plan& pl, cudaStream_t st) {
+  if (pl.cluster == 2 && MODE != MODE_WGRAD) {
+    if (pl.block_n == 128) return launch_one < MODE == MODE_WGRAD ? MODE_FPROP : MODE, 128, 2 > (L, pl, st);
+    return launch_one < MODE == MODE_WGRAD ? MODE_FPROP : MODE, 256, 2 > (L, pl, st);
+  }
   switch (pl.block_n) {
-    case 64: return launch_one<MODE, 64>(L, pl, st);
-    case 128: return launch_one<MODE, 128>(L, pl, st);
-    default: return launch_one<MODE, 256>(L, pl, st);
+    case 64: return launch_one<MODE, 64, 1>(L, pl, st);
+    case 128: return launch_one<MODE, 128, 1>(L, pl, st);
+    default: return launch_one<MODE, 256, 1>(L, pl, st);
   }
 }
 

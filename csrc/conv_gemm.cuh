@@ -90,7 +90,11 @@ struct ConvCfg {
   static constexpr int kThreads = 64 + 32 * kEpiWarps;
 };
 
-template <int MODE, int BLOCK_N>
+// CL = thread-block cluster size along the M-tile axis (1 or 2).  With CL = 2 the two CTAs work on
+// neighbouring M tiles of the same N tile and K range: each loads HALF of every weight (B) tile and TMA
+// multicasts it into both CTAs' shared memory, halving the L2 reads of the operand both need; a smem
+// stage is recycled only when both CTAs' MMAs have drained it (multicast tcgen05.commit).
+template <int MODE, int BLOCK_N, int CL>
 __global__ void __launch_bounds__(64 + 32 * 8, 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void* __restrict__ out,
                  const void* __restrict__ addend, float* __restrict__ scratch, unsigned int* __restrict__ tickets,
@@ -125,7 +129,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
   }
   if (warp == 1) {
     if (elect_one()) {
-      for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+      for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], CL); }
       mbar_init(tmem_full, 1);
       fence_mbar_init();
     }
@@ -133,8 +137,10 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     tmem_alloc<BLOCK_N>(tmem_ptr);
   }
   tc_fence_before();
-  __syncthreads();
+  if (CL > 1) cluster_sync_all(); else __syncthreads();     // peers' barriers exist before anyone signals them
   tc_fence_after();
+  const uint32_t crank = (CL > 1) ? cluster_ctarank() : 0u;
+  constexpr uint16_t kMcMask = (1u << CL) - 1u;
   const uint32_t tmem_base = *tmem_ptr;
   // PDL: everything above overlapped the previous kernel's tail; from here on we touch its outputs
   pdl_wait();
@@ -165,12 +171,23 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
           tma_load_4d(sA, &maps.act[te.map], &full_bar[stage], kb * 64, w0 + te.dw, h0 + te.dh, nn0);
           if (MODE == MODE_FPROP) {
             // weights [Cout rows][taps*Cin cols], K-major: one box of 64 cols x BLOCK_N rows
-            tma_load_2d(sB, &maps.other, &full_bar[stage], te.wtap * p.red_ch + kb * 64, n0);
+            if (CL == 1) {
+              tma_load_2d(sB, &maps.other, &full_bar[stage], te.wtap * p.red_ch + kb * 64, n0);
+            } else {          // my half of the rows, delivered to both CTAs
+              constexpr int kHalfRows = BLOCK_N / CL;
+              tma_load_2d_mc(sB + crank * kHalfRows * 128, &maps.other, &full_bar[stage],
+                             te.wtap * p.red_ch + kb * 64, n0 + (int)crank * kHalfRows, kMcMask);
+            }
           } else {
             // weights [Cout rows][taps*Cin cols]; B[n=ci, k=co] is MN-major: boxes of 64 ci x 64 co
 #pragma unroll
-            for (int j = 0; j < BLOCK_N / 64; ++j)
-              tma_load_2d(sB + j * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64, kb * 64);
+            for (int j = 0; j < BLOCK_N / 64; ++j) {
+              if (CL == 1)
+                tma_load_2d(sB + j * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64, kb * 64);
+              else if ((j % CL) == (int)crank)      // boxes dealt round-robin to the cluster's CTAs
+                tma_load_2d_mc(sB + j * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64,
+                               kb * 64, kMcMask);
+            }
           }
         } else {
           decode(it, w0, h0, nn0);
@@ -204,7 +221,8 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
           const uint64_t db = make_smem_desc_sw128(sB + k * b_kstep, p.b_lbo, p.b_sbo);
           umma_bf16(tmem_base, da, db, idesc, (it > it_begin || k > 0) ? 1u : 0u);
         }
-        umma_commit(&empty_bar[stage]);                 // frees the smem slot when these MMAs retire
+        if (CL == 1) umma_commit(&empty_bar[stage]);    // frees the smem slot when these MMAs retire
+        else umma_commit_mc(&empty_bar[stage], kMcMask);   // ... in every CTA that multicasts into it
         if (it == it_end - 1) umma_commit(tmem_full);   // accumulator complete
       }
       __syncwarp();
@@ -429,7 +447,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     tc_fence_before();
   }
 
-  __syncthreads();
+  if (CL > 1) cluster_sync_all(); else __syncthreads();     // a peer may still signal my barriers until it is done
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<BLOCK_N>(tmem_base);

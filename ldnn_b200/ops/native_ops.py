@@ -24,7 +24,7 @@ class ConvPlan:
                  x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, dw: Optional[torch.Tensor] = None,
                  addend: Optional[torch.Tensor] = None, accumulate: bool = False, block_n: int = 0, splits: int = 0,
                  workspace=None, desc_override=None, bn_sums: Optional[torch.Tensor] = None,
-                 atomic_out: bool = False, bn_bwd_fuse=None):
+                 atomic_out: bool = False, bn_bwd_fuse=None, cluster: int = 1):
         d = L.ConvDesc()
         d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
         d.block_n, d.splits, d.accumulate = block_n, splits, int(accumulate)
@@ -33,6 +33,7 @@ class ConvPlan:
         d.addend = 0 if addend is None else addend.data_ptr()
         d.bn_sums = 0 if bn_sums is None else bn_sums.data_ptr()
         d.atomic_out = int(atomic_out)
+        d.cluster = int(cluster)
         if bn_bwd_fuse is not None:        # (out, y, mean, invstd, sums, relu) of the layer that owns dx
             f_out, f_y, f_mean, f_is, f_sums, f_relu = bn_bwd_fuse
             d.fuse_out, d.fuse_y, d.fuse_mean = f_out.data_ptr(), f_y.data_ptr(), f_mean.data_ptr()

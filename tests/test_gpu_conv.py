@@ -120,3 +120,13 @@ def test_dgrad_fused_bn_backward_reduce(case, relu):
     want_a, want_b = d.sum(0), (d * xh).sum(0)
     assert torch.allclose(sums[:Cin], want_a, rtol=2e-3, atol=2e-3 * float(want_a.abs().max()))
     assert torch.allclose(sums[Cin:], want_b, rtol=2e-3, atol=2e-3 * float(want_b.abs().max()))
+
+
+@pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (64, 8, 8, 256, 256, 3, 1, 1),
+                                  (64, 16, 16, 128, 256, 3, 2, 1), (8, 14, 14, 256, 256, 3, 1, 1)])
+@pytest.mark.parametrize("splits", [1, 3])
+def test_cluster_multicast_weights(case, splits):
+    """Clusters of two M tiles: each CTA loads half of the weight tile and TMA-multicasts it to both."""
+    from ldnn_b200.ops import native_ops as K
+    assert _run(case, K.FPROP, cluster=2, block_n=128, splits=splits) < 1.5e-2
+    assert _run(case, K.DGRAD, cluster=2, block_n=128, splits=splits) < 1.5e-2
