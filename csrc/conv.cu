@@ -81,7 +81,7 @@ struct Launch {
   int covered_classes = 1;                  // dgrad: parity classes that have taps
 };
 struct Plan {
-  int mode, block_n, cluster = 1;
+  int mode, block_n, cluster = 1, lite = 0;
   std::vector<Launch> launches;
   void* out;
   const void* addend;
@@ -138,6 +138,7 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   LDNN_ARG(bn_ == 64 || bn_ == 128 || bn_ == 256, "block_n %d", bn_);
   LDNN_ARG(n_total % bn_ == 0, "N=%d not a multiple of block_n=%d", n_total, bn_);
   plan.mode = d.mode; plan.block_n = bn_;
+  plan.lite = d.lite ? 1 : 0;
   plan.cluster = (d.cluster == 2 && d.mode != MODE_WGRAD && bn_ >= 128) ? 2 : 1;
   plan.out = (d.mode == MODE_FPROP) ? d.y : (d.mode == MODE_DGRAD ? const_cast<void*>(d.x) : d.dw);
   plan.addend = d.addend ? d.addend : plan.out;
@@ -319,17 +320,20 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   return LDNN_OK;
 }
 
-template <int MODE, int BN, int CL>
+template <int MODE, int BN, int CL, bool LITE>
 static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
   using Cfg = ConvCfg<BN>;
+  constexpr int kSmem = LITE ? Cfg::kLiteSmemBytes : Cfg::kSmemBytes;
   static bool configured = false;
   if (!configured) {
-    LDNN_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<MODE, BN, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   Cfg::kSmemBytes));
+    LDNN_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<MODE, BN, CL, LITE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   kSmem));
     configured = true;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = L.grid; cfg.blockDim = dim3(Cfg::kThreads); cfg.dynamicSmemBytes = Cfg::kSmemBytes; cfg.stream = st;
+  cfg.gridDim = L.grid; cfg.stream = st;
+  cfg.blockDim = dim3(LITE ? Cfg::kLiteThreads : Cfg::kThreads);
+  cfg.dynamicSmemBytes = kSmem;
   cudaLaunchAttribute attr[2];
   int na = 0;
   if (pdl_enabled()) {
@@ -343,23 +347,30 @@ static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
     ++na;
   }
   cfg.attrs = attr; cfg.numAttrs = na;
-  LDNN_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<MODE, BN, CL>, L.maps, L.p, pl.out, pl.addend,
+  LDNN_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<MODE, BN, CL, LITE>, L.maps, L.p, pl.out, pl.addend,
                                pl.scratch ? pl.scratch + L.scratch_off : nullptr,
                                pl.tickets ? pl.tickets + L.ticket_off : nullptr, pl.stats, pl.fuse));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return LDNN_OK;
 }
 
+template <int MODE, int BN>
+static int launch_variant(const Launch& L, const Plan& pl, cudaStream_t st) {
+  if (pl.lite) return launch_one<MODE, BN, 1, true>(L, pl, st);
+  return launch_one<MODE, BN, 1, false>(L, pl, st);
+}
+
 template <int MODE>
 static int launch_bn(const Launch& L, const Plan& pl, cudaStream_t st) {
-  if (pl.cluster == 2 && MODE != MODE_WGRAD) {
-    if (pl.block_n == 128) return launch_one < MODE == MODE_WGRAD ? MODE_FPROP : MODE, 128, 2 > (L, pl, st);
-    return launch_one < MODE == MODE_WGRAD ? MODE_FPROP : MODE, 256, 2 > (L, pl, st);
+  if (pl.cluster == 2 && MODE != MODE_WGRAD) {      // cluster path: 128/256-wide tiles, full pipeline
+    constexpr int M2 = MODE == MODE_WGRAD ? MODE_FPROP : MODE;
+    if (pl.block_n == 128) return launch_one<M2, 128, 2, false>(L, pl, st);
+    return launch_one<M2, 256, 2, false>(L, pl, st);
   }
   switch (pl.block_n) {
-    case 64: return launch_one<MODE, 64, 1>(L, pl, st);
-    case 128: return launch_one<MODE, 128, 1>(L, pl, st);
-    default: return launch_one<MODE, 256, 1>(L, pl, st);
+    case 64: return launch_variant<MODE, 64>(L, pl, st);
+    case 128: return launch_variant<MODE, 128>(L, pl, st);
+    default: return launch_variant<MODE, 256>(L, pl, st);
   }
 }
 

@@ -86,6 +86,11 @@ struct ConvCfg {
   static constexpr int kBBytes = BLOCK_N * 64 * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  // 'lite' launch for large grids of short-K tiles: ~96 KB of stages and 4 epilogue warps, so two CTAs
+  // share an SM and one CTA's prologue/epilogue hides under the other's mainloop
+  static constexpr int kLiteStages = (BLOCK_N == 256) ? 2 : (BLOCK_N == 128 ? 3 : 4);
+  static constexpr int kLiteSmemBytes = kLiteStages * kStageBytes + 1024 + 256;
+  static constexpr int kLiteThreads = 64 + 32 * 4;
   static constexpr int kEpiWarps = 8;          // two warps per TMEM lane quarter, each takes half of the columns
   static constexpr int kThreads = 64 + 32 * kEpiWarps;
 };
@@ -94,13 +99,14 @@ struct ConvCfg {
 // neighbouring M tiles of the same N tile and K range: each loads HALF of every weight (B) tile and TMA
 // multicasts it into both CTAs' shared memory, halving the L2 reads of the operand both need; a smem
 // stage is recycled only when both CTAs' MMAs have drained it (multicast tcgen05.commit).
-template <int MODE, int BLOCK_N, int CL>
-__global__ void __launch_bounds__(64 + 32 * 8, 1)
+// LITE = short pipeline + 4 epilogue warps, two CTAs per SM (large grids of short-K tiles).
+template <int MODE, int BLOCK_N, int CL, bool LITE>
+__global__ void __launch_bounds__(LITE ? 192 : 320, LITE ? 2 : 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void* __restrict__ out,
                  const void* __restrict__ addend, float* __restrict__ scratch, unsigned int* __restrict__ tickets,
                  float* __restrict__ stats, const BnBwdFuse fuse) {
   using Cfg = ConvCfg<BLOCK_N>;
-  constexpr int kStages = Cfg::kStages;
+  constexpr int kStages = LITE ? Cfg::kLiteStages : Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
@@ -234,7 +240,8 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     const int row = q * 32 + lane_id();        // accumulator row == M index inside the tile
     const int et = (warp - 2) * 32 + lane_id();  // 0..255 epilogue thread id
     const int chalf = (warp - 2) >> 2;           // which half of the tile's columns this warp drains
-    constexpr int kColsPerWarp = BLOCK_N / 2;
+    constexpr int epi_threads = LITE ? 128 : 256;
+    constexpr int kColsPerWarp = BLOCK_N / (epi_threads >> 7);
     const int c_begin = chalf * kColsPerWarp, c_end = c_begin + kColsPerWarp;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
@@ -355,8 +362,8 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
       col_reduce(col0, a, b);
     };
     auto flush_stats = [&]() {
-      asm volatile("bar.sync 2, 256;" ::: "memory");
-      for (int idx = et; idx < 2 * BLOCK_N; idx += 256) {
+      asm volatile("bar.sync 2, %0;" ::"n"(epi_threads) : "memory");
+      for (int idx = et; idx < 2 * BLOCK_N; idx += epi_threads) {
         const int which = idx / BLOCK_N, col = idx % BLOCK_N;
         const float* src = red + (col >> 5) * 4 * 64 + which * 32 + (col & 31);
         const float t = src[0] + src[64] + src[128] + src[192];
@@ -396,7 +403,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
           part[(c / 4 + i) * 128 + row] = make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]),
                                                       __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(epi_threads) : "memory");
       if (et == 0) {
         __threadfence();                       // one fence per CTA publishes every epilogue thread's partial
         const unsigned int old = atomicAdd(&tickets[tile_lin], 1u);
@@ -404,7 +411,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
         if (last) __threadfence();
         *last_flag = last;
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(epi_threads) : "memory");
       if (*last_flag) {
         const float4* base = reinterpret_cast<const float4*>(scratch) + tile_lin * stride_splits * (BLOCK_N / 4) * 128;
 #pragma unroll 1

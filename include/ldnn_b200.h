@@ -40,6 +40,8 @@ typedef struct {
   unsigned int a_lbo, a_sbo, b_lbo, b_sbo; /* debug: override smem-descriptor strides (0 = default) */
   int cluster;         /* fprop/dgrad: 2 = thread-block clusters of two M tiles, weight tile TMA-multicast to both
                           (needs block_n >= 128 and an even number of M tiles); 0/1 = no cluster          */
+  int lite;            /* 1 = short pipeline (~96 KB smem) + 4 epilogue warps so two CTAs share an SM: for large
+                          grids of short-K tiles (one CTA's prologue/epilogue hides under the other's mainloop) */
   int atomic_out;      /* wgrad: split-K partial tiles are red.add'ed straight into dw (caller zeroes dw
                           once per step) instead of going through scratch + ticket; not bit-reproducible */
   float* bn_sums;      /* fprop, optional: fp32 [2][Cout]; the epilogue ADDS per-channel sum and sum of

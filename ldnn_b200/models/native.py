@@ -468,9 +468,11 @@ class _StepPlan:
             geo, xin = (n, ci.P, ci.Q, ci.kdim, u.cout, 1, 1, 0), self.col[u.conv_key]
         else:
             geo, xin = (n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad), self.act[u.src]
-        bn_, sp_ = K.tuned_conv_config(K.FPROP, geo, lambda b, s_: K.ConvPlan(K.FPROP, *geo, xin, w, yraw, bn_sums=fsum,
-                                                                          block_n=b, splits=s_), eng.autotune)
-        plan = K.ConvPlan(K.FPROP, *geo, xin, w, yraw, workspace=self.ws, bn_sums=fsum, block_n=bn_, splits=sp_)
+        bn_, sp_, lt_ = K.tuned_conv_config(
+            K.FPROP, geo, lambda b, s_, l_: K.ConvPlan(K.FPROP, *geo, xin, w, yraw, bn_sums=fsum, block_n=b, splits=s_,
+                                                       lite=l_), eng.autotune)
+        plan = K.ConvPlan(K.FPROP, *geo, xin, w, yraw, workspace=self.ws, bn_sums=fsum, block_n=bn_, splits=sp_,
+                          lite=lt_)
         self._add(plan.run, plan.num_launches)
         if fast:
             self._add(lambda: K.bn_fwd_apply_sums(yraw, fsum, gamma, beta, rm, rv, nbt, sm, si, res, out, M, Cc, u.relu,
@@ -521,11 +523,11 @@ class _StepPlan:
             geo = (n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad)
             xin = self.act[u.src]
         atomic = not eng.deterministic
-        bn_, sp_ = K.tuned_conv_config(K.WGRAD, geo, lambda b, s_: K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw,
-                                                                          atomic_out=atomic, block_n=b, splits=s_),
-                                       eng.autotune and atomic)
+        bn_, sp_, lt_ = K.tuned_conv_config(
+            K.WGRAD, geo, lambda b, s_, l_: K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, atomic_out=atomic,
+                                                       block_n=b, splits=s_, lite=l_), eng.autotune and atomic)
         wg = K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, workspace=self.ws, atomic_out=atomic, block_n=bn_,
-                        splits=sp_)
+                        splits=sp_, lite=lt_)
         if atomic and K.conv_query(K.WGRAD, *geo, block_n=bn_, splits=sp_)[0] > 0:   # split-K → red.add into a zeroed slice
             sl = eng.flat.by_key[u.conv_key + ".weight"]
             self.zero_ranges.append((sl.offset, sl.offset + sl.numel))
@@ -539,9 +541,9 @@ class _StepPlan:
         if not acc and not full_cover:
             self._add(lambda: dx.zero_(), 0)
             acc = True
-        bn_, sp_ = K.tuned_conv_config(K.DGRAD, geo, lambda b, s_: K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx,
-                                                                          accumulate=True, block_n=b, splits=s_),
-                                       eng.autotune)
+        bn_, sp_, lt_ = K.tuned_conv_config(
+            K.DGRAD, geo, lambda b, s_, l_: K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx, accumulate=True, block_n=b,
+                                                       splits=s_, lite=l_), eng.autotune)
         fuse = None
         if u.conv_key in self.fuse_into:
             ow = self.fuse_into[u.conv_key]
@@ -550,7 +552,7 @@ class _StepPlan:
                     eng.save_invstd[oo:oo + ow.cout],
                     eng.bn_sums[2 * eng.c_tot + 2 * oo:2 * eng.c_tot + 2 * oo + 2 * ow.cout], ow.relu)
         dg = K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx if acc else None, accumulate=acc, workspace=self.ws,
-                        block_n=bn_, splits=sp_, bn_bwd_fuse=fuse)
+                        block_n=bn_, splits=sp_, bn_bwd_fuse=fuse, lite=lt_)
         self._add(dg.run, dg.num_launches)
         written.add(u.src)
 

@@ -31,7 +31,7 @@ class ConvDesc(C.Structure):
                 ("splits", C.c_int), ("accumulate", C.c_int), ("x", C.c_void_p), ("w", C.c_void_p),
                 ("y", C.c_void_p), ("dw", C.c_void_p), ("addend", C.c_void_p), ("scratch", C.c_void_p),
                 ("tickets", C.c_void_p), ("a_lbo", C.c_uint), ("a_sbo", C.c_uint), ("b_lbo", C.c_uint),
-                ("b_sbo", C.c_uint), ("cluster", C.c_int), ("atomic_out", C.c_int), ("bn_sums", C.c_void_p), ("fuse_out", C.c_void_p), ("fuse_y", C.c_void_p),
+                ("b_sbo", C.c_uint), ("cluster", C.c_int), ("lite", C.c_int), ("atomic_out", C.c_int), ("bn_sums", C.c_void_p), ("fuse_out", C.c_void_p), ("fuse_y", C.c_void_p),
                 ("fuse_mean", C.c_void_p), ("fuse_invstd", C.c_void_p), ("fuse_sums", C.c_void_p),
                 ("fuse_relu", C.c_int)]
 

@@ -24,7 +24,7 @@ class ConvPlan:
                  x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, dw: Optional[torch.Tensor] = None,
                  addend: Optional[torch.Tensor] = None, accumulate: bool = False, block_n: int = 0, splits: int = 0,
                  workspace=None, desc_override=None, bn_sums: Optional[torch.Tensor] = None,
-                 atomic_out: bool = False, bn_bwd_fuse=None, cluster: int = 1):
+                 atomic_out: bool = False, bn_bwd_fuse=None, cluster: int = 1, lite: bool = False):
         d = L.ConvDesc()
         d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
         d.block_n, d.splits, d.accumulate = block_n, splits, int(accumulate)
@@ -34,6 +34,7 @@ class ConvPlan:
         d.bn_sums = 0 if bn_sums is None else bn_sums.data_ptr()
         d.atomic_out = int(atomic_out)
         d.cluster = int(cluster)
+        d.lite = int(lite)
         if bn_bwd_fuse is not None:        # (out, y, mean, invstd, sums, relu) of the layer that owns dx
             f_out, f_y, f_mean, f_is, f_sums, f_relu = bn_bwd_fuse
             d.fuse_out, d.fuse_y, d.fuse_mean = f_out.data_ptr(), f_y.data_ptr(), f_mean.data_ptr()
@@ -76,7 +77,7 @@ class ConvPlan:
 _TUNE_CACHE = {}
 
 
-def _time_plan(plan, iters=10, reps=3):
+def _time_plan(plan, iters=20, reps=3):
     best = float("inf")
     for _ in range(2):
         plan.run()
@@ -103,29 +104,34 @@ def conv_candidates(mode, geo, n_total):
 
 
 def tuned_conv_config(mode, geo, make_plan, enabled=True):
-    """Returns (block_n, splits) — (0, 0) = library heuristics.  `make_plan(block_n, splits)` must
-    build a runnable plan (private scratch) for timing."""
+    """Returns (block_n, splits, lite) — (0, 0, False) = library heuristics.  `make_plan(block_n,
+    splits, lite)` must build a runnable plan (private scratch) for timing.  `lite` (two CTAs per SM)
+    is tried only for grids of more than one wave."""
     if not enabled:
-        return 0, 0
+        return 0, 0, False
     key = (mode,) + tuple(geo)
     if key in _TUNE_CACHE:
         return _TUNE_CACHE[key]
     N, H, W, Cin, Cout, R, stride, pad = geo
     n_total = Cout if mode == FPROP else Cin
-    best_cfg, best_t = (0, 0), _time_plan(make_plan(0, 0))
-    seen = set()
-    for bn, sp in conv_candidates(mode, geo, n_total):
-        try:
-            plan = make_plan(bn, sp)
-        except L.LdnnError:
-            continue
-        sig = (bn, plan.grid)
-        if sig in seen or not (24 <= plan.grid[0] * plan.grid[1] * plan.grid[2] <= 1200):
-            continue
-        seen.add(sig)
-        t = _time_plan(plan)
-        if t < best_t * 0.97:                      # only leave the heuristic for a clear win
-            best_cfg, best_t = (bn, sp), t
+    base = make_plan(0, 0, False)
+    best_cfg, best_t = (0, 0, False), _time_plan(base)
+    seen = {(0, base.grid, False)}
+    cands = [(0, 0)] + conv_candidates(mode, geo, n_total)
+    for bn, sp in cands:
+        for lite in (False, True):
+            try:
+                plan = make_plan(bn, sp, lite)
+            except L.LdnnError:
+                continue
+            ctas = plan.grid[0] * plan.grid[1] * plan.grid[2]
+            sig = (bn, plan.grid, lite)
+            if sig in seen or not (24 <= ctas <= 20000) or (lite and ctas < 296) or (ctas > 1200 and sp > 1):
+                continue
+            seen.add(sig)
+            t = _time_plan(plan)
+            if t < best_t * 0.95:                  # only leave the heuristic for a clear win
+                best_cfg, best_t = (bn, sp, lite), t
     _TUNE_CACHE[key] = best_cfg
     return best_cfg
 

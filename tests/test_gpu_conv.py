@@ -130,3 +130,16 @@ def test_cluster_multicast_weights(case, splits):
     from ldnn_b200.ops import native_ops as K
     assert _run(case, K.FPROP, cluster=2, block_n=128, splits=splits) < 1.5e-2
     assert _run(case, K.DGRAD, cluster=2, block_n=128, splits=splits) < 1.5e-2
+
+
+@pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (8, 56, 56, 64, 256, 1, 1, 0), (6, 8, 8, 256, 512, 3, 2, 1)])
+@pytest.mark.parametrize("block_n", [64, 128, 256])
+def test_lite_launch_two_ctas_per_sm(case, block_n):
+    """Short-pipeline launch (fewer smem stages, 4 epilogue warps) used for large grids."""
+    from ldnn_b200.ops import native_ops as K
+    N, H, W, Cin, Cout, R, s, p = case
+    if Cout % block_n == 0:
+        assert _run(case, K.FPROP, lite=True, block_n=block_n) < 1.5e-2
+    if Cin % block_n == 0:
+        assert _run(case, K.DGRAD, lite=True, block_n=block_n) < 1.5e-2
+        assert _run(case, K.WGRAD, lite=True, block_n=block_n, atomic_out=True) < 5e-3

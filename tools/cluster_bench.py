@@ -19,8 +19,11 @@ for case in [(64, 16, 16, 128, 128, 3, 1, 1), (64, 8, 8, 256, 256, 3, 1, 1), (64
     y = torch.empty(N, P, Q, Cout, device="cuda", dtype=torch.bfloat16)
     dx = torch.zeros(N, H, W, Cin, device="cuda", dtype=torch.bfloat16)
     row = []
-    for cl in (1, 2):
-        pf = K.ConvPlan(K.FPROP, N, H, W, Cin, Cout, R, s, p, x, w.view(Cout, -1), y, block_n=128, cluster=cl)
-        pd = K.ConvPlan(K.DGRAD, N, H, W, Cin, Cout, R, s, p, dx, w.view(Cout, -1), dy, addend=dx, accumulate=True, block_n=128, cluster=cl)
-        row.append((graph_timeit(pf.run), graph_timeit(pd.run), pf.grid))
-    print(case, "fprop cl1/cl2 %.1f / %.1f us   dgrad %.1f / %.1f us  grid %s" % (row[0][0], row[1][0], row[0][1], row[1][1], row[0][2]))
+    dw = torch.zeros(Cout, R * R * Cin, device="cuda")
+    for cl, lite in ((1, False), (2, False), (1, True)):
+        pf = K.ConvPlan(K.FPROP, N, H, W, Cin, Cout, R, s, p, x, w.view(Cout, -1), y, block_n=128, cluster=cl, lite=lite)
+        pd = K.ConvPlan(K.DGRAD, N, H, W, Cin, Cout, R, s, p, dx, w.view(Cout, -1), dy, addend=dx, accumulate=True, block_n=128, cluster=cl, lite=lite)
+        pw = K.ConvPlan(K.WGRAD, N, H, W, Cin, Cout, R, s, p, x, None, dy, dw=dw, atomic_out=True, lite=lite)
+        row.append((graph_timeit(pf.run), graph_timeit(pd.run), graph_timeit(pw.run), pf.grid))
+    print(case, "fprop base/cluster2/lite %.1f / %.1f / %.1f us   dgrad %.1f / %.1f / %.1f   wgrad base/lite %.1f / %.1f  grid %s" % (
+        row[0][0], row[1][0], row[2][0], row[0][1], row[1][1], row[2][1], row[0][2], row[2][2], row[0][3]))
