@@ -458,8 +458,14 @@ im2col_stem_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col,
 }
 
 // ------------------------------------------------------------------ max pool NHWC bf16
-__global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int H,
-                                   int W, int C, int k, int stride, int pad, int P, int Q) {
+// Forward records the window position of the (first) maximum per output element, so backward is a
+// gather: every input pixel looks at the <= ceil(k/stride)^2 windows that cover it and takes the
+// gradient of those whose recorded position is this pixel (same tie-break as torch: first maximum).
+__global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                   uint8_t* __restrict__ idx, int N, int H, int W, int C, int k, int stride, int pad,
+                                   int P, int Q) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int c8 = C >> 3;
   const long long total = (long long)N * P * Q * c8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -468,8 +474,9 @@ __global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
     const long long pix = i / c8;
     const int q = (int)(pix % Q), p = (int)((pix / Q) % P), n = (int)(pix / ((long long)P * Q));
     float m[8];
+    uint8_t am[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+    for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; am[j] = 0; }
     for (int r = 0; r < k; ++r)
       for (int s = 0; s < k; ++s) {
         const int h = p * stride - pad + r, w = q * stride - pad + s;
@@ -477,16 +484,24 @@ __global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
         float f[8];
         bf16x8_to_float(*reinterpret_cast<const uint4*>(x + (((size_t)n * H + h) * W + w) * C + cg * 8), f);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], f[j]);
+        for (int j = 0; j < 8; ++j)
+          if (f[j] > m[j]) { m[j] = f[j]; am[j] = (uint8_t)(r * k + s); }
       }
     reinterpret_cast<uint4*>(y)[i] = float_to_bf16x8(m);
+    if (idx) {
+      uint2 packed;
+      packed.x = am[0] | (am[1] << 8) | (am[2] << 16) | ((uint32_t)am[3] << 24);
+      packed.y = am[4] | (am[5] << 8) | (am[6] << 16) | ((uint32_t)am[7] << 24);
+      reinterpret_cast<uint2*>(idx)[i] = packed;
+    }
   }
 }
 
-// dx[h,w] = sum over windows containing (h,w) whose max equals x[h,w] (first-match tie-break as torch)
-__global__ void maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
-                                   const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int H,
-                                   int W, int C, int k, int stride, int pad, int P, int Q) {
+__global__ void maxpool_bwd_kernel(const uint8_t* __restrict__ idx, const __nv_bfloat16* __restrict__ dy,
+                                   __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int k, int stride,
+                                   int pad, int P, int Q) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int c8 = C >> 3;
   const long long total = (long long)N * H * W * c8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -494,28 +509,24 @@ __global__ void maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __
     const int cg = (int)(i % c8);
     const long long pix = i / c8;
     const int w = (int)(pix % W), h = (int)((pix / W) % H), n = (int)(pix / ((long long)H * W));
-    float xv[8], acc[8];
-    bf16x8_to_float(reinterpret_cast<const uint4*>(x)[i], xv);
+    float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-    for (int p = max(0, (h + pad - k + stride) / stride); p <= min(P - 1, (h + pad) / stride); ++p)
-      for (int q = max(0, (w + pad - k + stride) / stride); q <= min(Q - 1, (w + pad) / stride); ++q) {
-        const size_t o = (((size_t)n * P + p) * Q + q) * C + cg * 8;
-        float yv[8], gv[8];
-        bf16x8_to_float(*reinterpret_cast<const uint4*>(y + o), yv);
-        bf16x8_to_float(*reinterpret_cast<const uint4*>(dy + o), gv);
-        // first-match: (h,w) must be the first window element (row-major) equal to the max
+    const int p_lo = max(0, (h + pad - k + stride) / stride), p_hi = min(P - 1, (h + pad) / stride);
+    const int q_lo = max(0, (w + pad - k + stride) / stride), q_hi = min(Q - 1, (w + pad) / stride);
+    for (int p = p_lo; p <= p_hi; ++p)
+      for (int q = q_lo; q <= q_hi; ++q) {
+        const int r = h - (p * stride - pad), s = w - (q * stride - pad);
+        if (r < 0 || r >= k || s < 0 || s >= k) continue;
+        const uint32_t me = (uint32_t)(r * k + s);
+        const size_t o = (((size_t)n * P + p) * Q + q) * c8 + cg;
+        const uint2 packed = reinterpret_cast<const uint2*>(idx)[o];
+        float g[8];
+        bf16x8_to_float(reinterpret_cast<const uint4*>(dy)[o], g);
+#pragma unroll
         for (int j = 0; j < 8; ++j) {
-          if (xv[j] != yv[j]) continue;
-          bool first = true;
-          for (int r = 0; r < k && first; ++r)
-            for (int s = 0; s < k; ++s) {
-              const int hh = p * stride - pad + r, ww = q * stride - pad + s;
-              if (hh == h && ww == w) { r = k; break; }
-              if (hh < 0 || hh >= H || ww < 0 || ww >= W) continue;
-              if (__bfloat162float(x[(((size_t)n * H + hh) * W + ww) * C + cg * 8 + j]) == yv[j]) { first = false; break; }
-            }
-          if (first) acc[j] += gv[j];
+          const uint32_t a = ((j < 4 ? packed.x : packed.y) >> (8 * (j & 3))) & 0xffu;
+          if (a == me) acc[j] += g[j];
         }
       }
     reinterpret_cast<uint4*>(dx)[i] = float_to_bf16x8(acc);
@@ -661,26 +672,26 @@ extern "C" int ldnn_im2col_stem(const float* x, void* col, int N, int C, int H, 
   return LDNN_OK;
 }
 
-extern "C" int ldnn_maxpool_fwd(const void* x, void* y, int N, int H, int W, int C, int k, int stride, int pad,
-                                void* stream) {
+extern "C" int ldnn_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
+                                int pad, void* stream) {
+  LDNN_ARG(C % 8 == 0 && k * k <= 255, "maxpool: C=%d k=%d", C, k);
   const int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
   const long long total = (long long)N * P * Q * (C / 8);
-  maxpool_fwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C, k, stride, pad, P, Q);
+  LDNN_CUDA(launch_pdl(maxpool_fwd_kernel, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream,
+                       (const __nv_bfloat16*)x, (__nv_bfloat16*)y, (uint8_t*)idx, N, H, W, C, k, stride, pad, P, Q));
   COUNT_LAUNCH();
-  LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
 
-extern "C" int ldnn_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C,
-                                int k, int stride, int pad, void* stream) {
+extern "C" int ldnn_maxpool_bwd(const void* idx, const void* dy, void* dx, int N, int H, int W, int C, int k,
+                                int stride, int pad, void* stream) {
+  LDNN_ARG(idx != nullptr && C % 8 == 0, "maxpool backward needs the argmax map written by the forward pass");
   const int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
   const long long total = (long long)N * H * W * (C / 8);
-  maxpool_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, k,
-      stride, pad, P, Q);
+  LDNN_CUDA(launch_pdl(maxpool_bwd_kernel, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream,
+                       (const uint8_t*)idx, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, k, stride, pad, P,
+                       Q));
   COUNT_LAUNCH();
-  LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
 

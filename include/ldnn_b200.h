@@ -122,10 +122,13 @@ int ldnn_bn_bwd_reduce_sums(const void* dout, const void* out, const void* y, co
 int ldnn_bn_bwd_apply_sums(const void* dout, const void* out, const void* y, const float* save_mean,
                            const float* save_invstd, const float* gamma, const float* sums, void* dy_raw, void* dres,
                            float* dgamma, float* dbeta, int M, int C, int relu, int res_accumulate, void* stream);
-/* 3x3/s2/p1-style max pool on NHWC bf16 (+ backward), ResNet-50 stem */
-int ldnn_maxpool_fwd(const void* x, void* y, int N, int H, int W, int C, int k, int stride, int pad, void* stream);
-int ldnn_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, int k,
-                     int stride, int pad, void* stream);
+/* 3x3/s2/p1-style max pool on NHWC bf16 (ResNet-50 stem).  Forward also records, per output element, the
+ * window position of its (first) maximum in idx (uint8 [N,P,Q,C], may be NULL for inference); backward
+ * gathers dy through that map. */
+int ldnn_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride, int pad,
+                     void* stream);
+int ldnn_maxpool_bwd(const void* idx, const void* dy, void* dx, int N, int H, int W, int C, int k, int stride,
+                     int pad, void* stream);
 
 /* ------------------------------------------------------------------ head (K-HEAD)
  * global-avg-pool + linear + softmax cross-entropy (+ correct count, dlogits, d_act, fc grads)

@@ -357,6 +357,7 @@ class _StepPlan:
         self.bn_ticket = torch.zeros(4, dtype=torch.int32, device=dev)
 
         # ---- forward ----
+        self.pool_idx = {}
         self.zero_ranges = []          # flat-grad ranges that atomic split-K wgrads accumulate into
         zero_slot = len(self.ops)
         if self.training and not eng.deterministic:
@@ -367,7 +368,10 @@ class _StepPlan:
             elif isinstance(u, MaxPool):
                 H, Wd, Cc = eng.slot_shape[u.src]
                 xs, ys = self.act[u.src], self.act[u.dst]
-                self._add(lambda xs=xs, ys=ys, H=H, Wd=Wd, Cc=Cc, u=u: K.maxpool_fwd(xs, ys, n, H, Wd, Cc, u.k, u.stride, u.pad))
+                ix = torch.zeros(ys.numel(), dtype=torch.uint8, device=dev) if self.training else None
+                self.pool_idx[u.dst] = ix
+                self._add(lambda xs=xs, ys=ys, ix=ix, H=H, Wd=Wd, Cc=Cc, u=u: K.maxpool_fwd(xs, ys, ix, n, H, Wd, Cc, u.k,
+                                                                                        u.stride, u.pad))
             elif isinstance(u, Head):
                 H, Wd, Cc = eng.slot_shape[u.src]
                 a = self.act[u.src]
@@ -377,7 +381,8 @@ class _StepPlan:
                 gb = G(u.fc_key + ".bias") if self.training else None
                 self._add(lambda a=a, da=da, fw=fw, fb=fb, gw=gw, gb=gb, H=H, Wd=Wd, Cc=Cc, u=u: K.head_fwd_bwd(
                     a, n, H * Wd, Cc, u.num_classes, fw, fb, self.labels, self.pooled, self.logits, self.dlogits,
-                    self.loss_n, self.correct_n, self.pred, da, gw, gb, self.loss, self.correct, self.training), 2)
+                    self.loss_n, self.correct_n, self.pred, da, gw, gb, self.loss, self.correct, self.training),
+                    2 if u.num_classes <= 64 else (5 if self.training else 4))
         if not self.training:
             return
         # ---- backward ----
@@ -426,9 +431,9 @@ class _StepPlan:
             elif isinstance(u, MaxPool):
                 H, Wd, Cc = eng.slot_shape[u.src]
                 assert u.src not in written, "max-pool input with gradient fan-in is not supported"
-                xs, ys, dys, dxs = self.act[u.src], self.act[u.dst], self.dact[u.dst], self.dact[u.src]
-                self._add(lambda xs=xs, ys=ys, dys=dys, dxs=dxs, H=H, Wd=Wd, Cc=Cc, u=u: K.maxpool_bwd(
-                    xs, ys, dys, dxs, n, H, Wd, Cc, u.k, u.stride, u.pad))
+                ix, dys, dxs = self.pool_idx[u.dst], self.dact[u.dst], self.dact[u.src]
+                self._add(lambda ix=ix, dys=dys, dxs=dxs, H=H, Wd=Wd, Cc=Cc, u=u: K.maxpool_bwd(
+                    ix, dys, dxs, n, H, Wd, Cc, u.k, u.stride, u.pad))
                 written.add(u.src)
         close_bucket(force=True)
         assert prev_lo == 0, "backward did not produce every gradient"

@@ -25,6 +25,7 @@ class ConvPlan:
                  addend: Optional[torch.Tensor] = None, accumulate: bool = False, block_n: int = 0, splits: int = 0,
                  workspace=None, desc_override=None, bn_sums: Optional[torch.Tensor] = None,
                  atomic_out: bool = False, bn_bwd_fuse=None, cluster: int = 1, lite: bool = False):
+        self.mode = mode
         d = L.ConvDesc()
         d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
         d.block_n, d.splits, d.accumulate = block_n, splits, int(accumulate)
@@ -226,13 +227,12 @@ def bn_bwd_apply_sums(dout, out, y, save_mean, save_invstd, gamma, sums, dy_raw,
                                            L.ptr(dbeta), M, Cc, int(relu), int(res_accumulate), L.stream_ptr()))
 
 
-def maxpool_fwd(x, y, N, H, W, Cc, k, stride, pad):
-    L.check(L.lib().ldnn_maxpool_fwd(L.ptr(x), L.ptr(y), N, H, W, Cc, k, stride, pad, L.stream_ptr()))
+def maxpool_fwd(x, y, idx, N, H, W, Cc, k, stride, pad):
+    L.check(L.lib().ldnn_maxpool_fwd(L.ptr(x), L.ptr(y), L.ptr(idx), N, H, W, Cc, k, stride, pad, L.stream_ptr()))
 
 
-def maxpool_bwd(x, y, dy, dx, N, H, W, Cc, k, stride, pad):
-    L.check(L.lib().ldnn_maxpool_bwd(L.ptr(x), L.ptr(y), L.ptr(dy), L.ptr(dx), N, H, W, Cc, k, stride, pad,
-                                     L.stream_ptr()))
+def maxpool_bwd(idx, dy, dx, N, H, W, Cc, k, stride, pad):
+    L.check(L.lib().ldnn_maxpool_bwd(L.ptr(idx), L.ptr(dy), L.ptr(dx), N, H, W, Cc, k, stride, pad, L.stream_ptr()))
 
 
 def head_fwd_bwd(act, N, HW, Cc, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,

@@ -191,3 +191,22 @@ def test_conv_fused_stats_and_sums_bn(case, use_res):
     K.bn_fwd_apply_sums(y, None, gamma, beta, rm, rv, nbt, sm, si, None, out, M, C, False, False)
     ref = F.batch_norm(y.view(M, C).float(), rm, rv, gamma, beta, False, 0.1, 1e-5)
     assert torch.allclose(out.float(), ref, atol=4e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("N,H,W,C,k,s,p", [(4, 112, 112, 64, 3, 2, 1), (3, 9, 7, 128, 3, 2, 1), (2, 8, 8, 64, 2, 2, 0)])
+def test_maxpool_forward_backward(N, H, W, C, k, s, p):
+    from ldnn_b200.ops import native_ops as K
+    g = torch.Generator().manual_seed(H)
+    x = torch.randn(N, H, W, C, generator=g).cuda().bfloat16()
+    P, Q = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
+    y = torch.empty(N, P, Q, C, device="cuda", dtype=torch.bfloat16)
+    idx = torch.zeros(N * P * Q * C, device="cuda", dtype=torch.uint8)
+    dy = torch.randn(N, P, Q, C, generator=g).cuda().bfloat16()
+    dx = torch.empty(N, H, W, C, device="cuda", dtype=torch.bfloat16)
+    K.maxpool_fwd(x, y, idx, N, H, W, C, k, s, p)
+    K.maxpool_bwd(idx, dy, dx, N, H, W, C, k, s, p)
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    yr = F.max_pool2d(xr, k, s, p)
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    assert torch.equal(y.float(), yr.detach().permute(0, 2, 3, 1))
+    assert torch.allclose(dx.float(), xr.grad.permute(0, 2, 3, 1), atol=2e-2, rtol=2e-2)
