@@ -372,9 +372,12 @@ extern "C" int ldnn_head_fwd_bwd(const void* act, int N, int HW, int C, int clas
                        C, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,
                        (__nv_bfloat16*)dact, training, 1.f / (float)N));
   g_launches.fetch_add(1);
-  LDNN_CUDA(launch_pdl(head_reduce_kernel, dim3((C + 127) / 128), dim3(128), staged ? stage_bytes : (size_t)0,
-                       (cudaStream_t)stream, (const float*)pooled, (const float*)dlogits, (const float*)loss_n,
-                       (const float*)correct_n, N, C, classes, dfc_w, dfc_b, loss_out, correct_out, training, staged));
+  // fc gradients + batch totals on a (channel tile x class group) grid: 2-D parallelism instead of 8 CTAs
+  (void)staged;
+  LDNN_CUDA(launch_pdl(head_fcgrad_kernel, dim3(training ? (C + 127) / 128 : 1, training ? (classes + 7) / 8 : 1),
+                       dim3(128), (size_t)N * 8 * sizeof(float), (cudaStream_t)stream, (const float*)pooled,
+                       (const float*)dlogits, (const float*)loss_n, (const float*)correct_n, N, C, classes, dfc_w, dfc_b,
+                       loss_out, correct_out, training));
   g_launches.fetch_add(1);
   return LDNN_OK;
 }
