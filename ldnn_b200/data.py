@@ -257,19 +257,38 @@ class DeviceFeeder:
         self.loader, self.device = loader, device
         self.cuda = device.type == "cuda"
         self.stream = torch.cuda.Stream(device) if self.cuda else None
+        # two pinned staging slots, reused (a fresh pin_memory() per batch costs a cudaHostAlloc each time)
+        self._pin = [dict(), dict()]
+        self._done = [None, None]
+        self._slot = 0
 
     def __len__(self):
         return len(self.loader)
 
+    def _pinned(self, slot: int, t: torch.Tensor) -> torch.Tensor:
+        key = (tuple(t.shape), t.dtype)
+        buf = self._pin[slot].get(key)
+        if buf is None:
+            buf = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+            self._pin[slot][key] = buf
+        return buf
+
     def _stage(self, x, y):
         if not self.cuda:
             return x, y, None
-        xp, yp = x.pin_memory(), y.pin_memory()
+        slot = self._slot
+        self._slot ^= 1
+        if self._done[slot] is not None:
+            self._done[slot].synchronize()          # the copy that last used this slot has finished
+        xp, yp = self._pinned(slot, x), self._pinned(slot, y)
+        xp.copy_(x)
+        yp.copy_(y)
         with torch.cuda.stream(self.stream):
             xd = xp.to(self.device, non_blocking=True)
             yd = yp.to(self.device, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(self.stream)
+        self._done[slot] = ev
         return xd, yd, (ev, xp, yp)
 
     def __iter__(self):
