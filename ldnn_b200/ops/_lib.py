@@ -59,14 +59,23 @@ X_UPDATE, X_SELFMIX, X_CAST = 1, 2, 4
 
 
 def available() -> bool:
-    return os.path.exists(LIB_PATH)
+    """True when the native library exists or can be built here (nvcc present)."""
+    if os.path.exists(LIB_PATH):
+        return True
+    import shutil
+    return shutil.which("nvcc") is not None or os.path.exists("/usr/local/cuda/bin/nvcc")
 
 
 def lib():
     global _lib
     if _lib is None:
         if not os.path.exists(LIB_PATH):
-            raise LdnnError(f"{LIB_PATH} is missing — run `python -m ldnn_b200.build` (or __graft_entry__.build())")
+            try:                                   # in-tree build on first use (nvcc needed, ~30 s)
+                from ..build import build as _build
+                _build(verbose=False)
+            except Exception as e:
+                raise LdnnError(f"{LIB_PATH} is missing and could not be built ({e}) — run "
+                                f"`python -m ldnn_b200.build` (or __graft_entry__.build())")
         _lib = C.CDLL(LIB_PATH)
         _lib.ldnn_last_error.restype = C.c_char_p
         _lib.ldnn_launch_count.restype = C.c_ulonglong
