@@ -283,8 +283,22 @@ def run_reference(a):
     dist.destroy_process_group()
 
 
+def _self_launch(a):
+    """`python bench.py --gpus N` without a launcher: re-exec under torch.distributed.run."""
+    import socket
+    import subprocess
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={a.gpus}", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__)] + sys.argv[1:]
+    raise SystemExit(subprocess.call(cmd))
+
+
 if __name__ == "__main__":
     args = parse()
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        _self_launch(args)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -1,0 +1,79 @@
+"""Flag surface, schedule resolution, checkpoint round trip and the PNG rasteriser (CPU)."""
+import json
+import struct
+import zlib
+
+import numpy as np
+import torch
+
+from ldnn_b200.config import Config, build_parser, parse_args, resolve
+
+
+def test_reference_flags_and_defaults():
+    cfg = parse_args([], topology="ring", balance="balanced")
+    assert (cfg.backend, cfg.epochs_local, cfg.epochs_global, cfg.batch_size, cfg.lr) == ("gloo", 5, 20, 64, 1e-3)
+    assert (cfg.time_limit, cfg.prev_fraction, cfg.next_fraction, cfg.local_weight, cfg.fixed_ratio) == (60, 0.5, 0.5, 0.5, 0.5)
+    assert (cfg.aggregation_type, cfg.aggregation_by) == ("equal", "gradients")
+    # dead upstream flags still parse
+    cfg = parse_args(["--local-rank", "3", "--gpu_weight", "7", "--dist-url", "tcp://x:1", "--backend", "nccl"])
+    assert cfg.local_rank == 3 and cfg.gpu_weight == 7 and cfg.dist_url == "tcp://x:1"
+    names = {a.dest for a in build_parser()._actions}
+    for flag in ["epochs_local", "epochs_global", "batch_size", "lr", "time_limit", "prev_fraction", "next_fraction",
+                 "aggregation_type", "aggregation_by", "local_weight", "fixed_ratio", "gpu_weight", "dist_url", "backend"]:
+        assert flag in names, flag
+
+
+def test_schedule_resolution():
+    c = resolve(Config(topology="ring", sync="global_epoch"))
+    assert c.semantics == "gossip" and c.apply_exchanged_grads is False          # reference behaviour
+    c = resolve(Config(topology="ring", sync="step"))
+    assert c.semantics == "allreduce" and c.apply_exchanged_grads is True        # product path
+    c = resolve(Config(topology="allreduce", sync="global_epoch"))
+    assert c.semantics == "allreduce"
+    # sampling with replacement: BalAR/BalR without, BalDR and every Dis* with
+    assert resolve(Config(topology="ring", balance="balanced")).replace is False
+    assert resolve(Config(topology="double_ring", balance="balanced")).replace is True
+    assert resolve(Config(topology="allreduce", balance="disbalanced")).replace is True
+
+
+def test_checkpoint_roundtrip_torch_engine(tmp_path):
+    from ldnn_b200.engine import OptimConfig, TorchEngine
+    from ldnn_b200.utils.checkpoint import load_checkpoint, save_checkpoint
+    from test_flat_optimizer import tiny_spec
+    torch.manual_seed(0)
+    a = TorchEngine(tiny_spec(), "cpu", OptimConfig(lr=1e-2))
+    x, y = torch.randn(8, 3, 8, 8), torch.randint(0, 10, (8,))
+    for _ in range(3):
+        a.train_step(x, y)
+    a.scheduler_step()
+    path = str(tmp_path / "ck.pt")
+    save_checkpoint(path, a, epoch=5)
+    b = TorchEngine(tiny_spec(), "cpu", OptimConfig(lr=1e-2))
+    assert load_checkpoint(path, b) == 5
+    assert torch.equal(a.flat.params, b.flat.params) and torch.equal(a.flat.m, b.flat.m) and torch.equal(a.flat.v, b.flat.v)
+    assert (a.flat.step, a.flat.epoch) == (b.flat.step, b.flat.epoch)
+    la, _ = a.train_step(x, y)
+    lb, _ = b.train_step(x, y)
+    assert torch.equal(la, lb)
+    # a bare upstream-style state_dict file loads too
+    torch.save(a.state_dict(), str(tmp_path / "sd.pt"))
+    c = TorchEngine(tiny_spec(), "cpu", OptimConfig())
+    assert load_checkpoint(str(tmp_path / "sd.pt"), c) == 0
+    assert torch.equal(c.flat.params, a.flat.params)
+
+
+def test_rasteriser_writes_valid_png(tmp_path):
+    from ldnn_b200.utils import viz
+    viz.plot_metrics_global(3, [1.0, 0.5, 0.2], [10, 50, 80], [1.2, 0.9, 0.7], [9, 40, 60], output_folder=str(tmp_path))
+    viz.plot_loss_distribution_per_epoch([[0.1, 0.2, 0.9], [0.05, 0.1]], output_folder=str(tmp_path))
+    viz.plot_time_throughput([1.0, 0.9], [1000, 1100], [5.0, 4.0], output_folder=str(tmp_path))
+    for name in ("training_metrics.png", "loss_distribution_per_epoch.png", "time_throughput.png"):
+        raw = (tmp_path / name).read_bytes()
+        assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+        w, h = struct.unpack(">II", raw[16:24])
+        assert (w, h) == (1600, 1000) or w > 100          # builtin canvas (matplotlib, if present, picks its own)
+        # IDAT decompresses to h rows of 1 + 3*w bytes for the builtin writer
+        if (w, h) == (1600, 1000):
+            i = raw.index(b"IDAT")
+            n = struct.unpack(">I", raw[i - 4:i])[0]
+            assert len(zlib.decompress(raw[i + 4:i + 4 + n])) == h * (1 + 3 * w)
