@@ -88,62 +88,6 @@ head_sample_kernel(const __nv_bfloat16* __restrict__ act, int HW, int C, int cla
   }
 }
 
-// fc gradients (deterministic sums over the batch) + batch loss / correct totals
-__global__ void __launch_bounds__(256)
-head_reduce_kernel(const float* __restrict__ pooled, const float* __restrict__ dlogits,
-                   const float* __restrict__ loss_n, const float* __restrict__ correct_n, int N, int C, int classes,
-                   float* __restrict__ dfc_w, float* __restrict__ dfc_b, float* __restrict__ loss_out,
-                   float* __restrict__ correct_out, int training, int staged) {
-  pdl_wait();
-  pdl_launch_dependents();
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  extern __shared__ float s_stage[];       // dlogits [N][classes] when it fits in smem
-  const float* s_dl = staged ? s_stage : dlogits;
-  if (training) {
-    if (staged) {
-      for (int i = threadIdx.x; i < N * classes; i += blockDim.x) s_stage[i] = dlogits[i];
-      __syncthreads();
-    }
-    if (c < C) {
-      // classes handled 8 at a time: pooled[n][c] is read once per group (coalesced over c)
-      for (int j0 = 0; j0 < classes; j0 += 8) {
-        float acc[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-        for (int n0 = 0; n0 < N; n0 += 8) {                 // 8 independent loads in flight per thread
-          float pv[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) pv[u] = (n0 + u < N) ? pooled[(size_t)(n0 + u) * C + c] : 0.f;
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            if (n0 + u >= N) break;
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if (j0 + j < classes) acc[j] += s_dl[(n0 + u) * classes + j0 + j] * pv[u];
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (j0 + j < classes) dfc_w[(size_t)(j0 + j) * C + c] = acc[j];
-      }
-    }
-  }
-  if (blockIdx.x == 0) {
-    if (training)
-      for (int j = threadIdx.x; j < classes; j += blockDim.x) {
-        float s = 0.f;
-        for (int n = 0; n < N; ++n) s += dlogits[(size_t)n * classes + j];
-        dfc_b[j] = s;
-      }
-    if (threadIdx.x < 32) {
-      float l = 0.f, k = 0.f;
-      for (int n = threadIdx.x; n < N; n += 32) { l += loss_n[n]; k += correct_n[n]; }
-      l = warp_sum(l); k = warp_sum(k);
-      if (threadIdx.x == 0) { *loss_out = l / (float)N; *correct_out = k; }
-    }
-  }
-}
-
 // ------------------------------------------------------------------ wide head (ImageNet-size fc)
 // With ~1000 classes the per-sample kernel above re-reads the whole fc weight for every sample
 // (1.7 ms for ResNet-50 at batch 32).  The wide path keeps the same math but tiles it so that the
@@ -365,15 +309,12 @@ extern "C" int ldnn_head_fwd_bwd(const void* act, int N, int HW, int C, int clas
     g_launches.fetch_add(launched + 1);
     return LDNN_OK;
   }
-  const size_t stage_bytes = (size_t)N * classes * sizeof(float);
-  const int staged = stage_bytes <= 40 * 1024;
   const size_t smem = (size_t)(C + 2 * classes) * sizeof(float);
   LDNN_CUDA(launch_pdl(head_sample_kernel, dim3(N), dim3(256), smem, (cudaStream_t)stream, (const __nv_bfloat16*)act, HW,
                        C, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,
                        (__nv_bfloat16*)dact, training, 1.f / (float)N));
   g_launches.fetch_add(1);
-  // fc gradients + batch totals on a (channel tile x class group) grid: 2-D parallelism instead of 8 CTAs
-  (void)staged;
+  // fc gradients + batch totals on a (channel tile x class group) grid
   LDNN_CUDA(launch_pdl(head_fcgrad_kernel, dim3(training ? (C + 127) / 128 : 1, training ? (classes + 7) / 8 : 1),
                        dim3(128), (size_t)N * 8 * sizeof(float), (cudaStream_t)stream, (const float*)pooled,
                        (const float*)dlogits, (const float*)loss_n, (const float*)correct_n, N, C, classes, dfc_w, dfc_b,
