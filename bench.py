@@ -115,14 +115,16 @@ def run_ours(a):
     def launches_now():
         return (L.launch_count() if L.available() else 0) + getattr(engine, "graph_kernel_launches", 0)
     l0 = launches_now()
-    with ClockSampler(dev.index or 0) as clk:
-        barrier_sync(dev)
-        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0.record()
-        epoch(a.steps)
-        t1.record()
-        barrier_sync(dev)
-        ms = t0.elapsed_time(t1)
+    # clocks / throttle reasons are sampled across BOTH timed regions (device-timed + end-to-end)
+    clk = ClockSampler(dev.index or 0, period_s=0.05)
+    clk.__enter__()
+    barrier_sync(dev)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    epoch(a.steps)
+    t1.record()
+    barrier_sync(dev)
+    ms = t0.elapsed_time(t1)
     launches = launches_now() - l0        # eager launches + kernels replayed from the step's CUDA graphs
     ms = max_over_ranks(ms, dev)
 
@@ -158,6 +160,7 @@ def run_ours(a):
     e2e_epoch(a.steps)
     barrier_sync(dev)
     e2e_s = max_over_ranks(time.perf_counter() - w0, dev)
+    clk.__exit__(None, None, None)
 
     if hasattr(ex, "check"):
         ex.check()
