@@ -135,9 +135,9 @@ def get_loaders(batch_size, world_size, rank, model, device, fixed_ratio=None, *
 def get_dataset_partition(dataset, rank, efficiency_ratios, fixed_ratio=None):
     if fixed_ratio is None:
         idx = D.partition_balanced(len(dataset), rank, efficiency_ratios)
-        return D.Loader(dataset, idx, 1).dataset, idx
+        return D.SubsetView(dataset, idx), list(idx)
     idx, fixed = D.partition_class_skew(dataset.labels, rank, efficiency_ratios, fixed_ratio)
-    return dataset, idx, fixed
+    return D.SubsetView(dataset, idx), list(idx), fixed
 
 
 def get_next_dataset_partition(dataset, prev_indices, prev_fraction, next_fraction, epoch_duration,
@@ -145,7 +145,7 @@ def get_next_dataset_partition(dataset, prev_indices, prev_fraction, next_fracti
     tot = float(epoch_duration_tensor.item()) if torch.is_tensor(epoch_duration_tensor) else float(epoch_duration_tensor)
     idx = D.next_partition(len(dataset), prev_indices, prev_fraction, next_fraction, epoch_duration / max(tot, 1e-12),
                            replace, labels=dataset.labels, fixed_classes=fixed_classes, fixed_ratio=fixed_ratio)
-    return dataset, idx
+    return D.SubsetView(dataset, idx), list(idx)
 
 
 def get_subset_loaders(trainset, valset, train_indices, val_indices, batch_size, prev_fraction, next_fraction,

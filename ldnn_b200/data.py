@@ -49,6 +49,11 @@ class ArrayDataset:
     def __len__(self) -> int:
         return len(self.labels)
 
+    def __getitem__(self, i: int):
+        """(image, label) like a torch Dataset — for code that indexes samples one by one."""
+        x, y = self.batch(np.asarray([int(i)]))
+        return x[0], int(y[0])
+
     def batch(self, idx: np.ndarray) -> Tuple[torch.Tensor, torch.Tensor]:
         it = torch.as_tensor(np.asarray(idx, dtype=np.int64))
         x = self.images.index_select(0, it)
@@ -67,6 +72,24 @@ class ArrayDataset:
         ds = ArrayDataset(self.images.index_select(0, it), self.labels[np.asarray(idx)], None, None, self.augment)
         ds.mean, ds.std = self.mean, self.std
         return ds
+
+
+class SubsetView:
+    """Index view of an :class:`ArrayDataset` with the surface of ``torch.utils.data.Subset``
+    (``.dataset``, ``.indices``, ``len``, ``[i]``) — what upstream's ``get_dataset_partition`` returns."""
+
+    def __init__(self, dataset: ArrayDataset, indices):
+        self.dataset, self.indices = dataset, np.asarray(indices, dtype=np.int64)
+        self.labels = dataset.labels[self.indices]
+
+    def __len__(self) -> int:
+        return len(self.indices)
+
+    def __getitem__(self, i: int):
+        return self.dataset[int(self.indices[i])]
+
+    def batch(self, idx: np.ndarray):
+        return self.dataset.batch(self.indices[np.asarray(idx, dtype=np.int64)])
 
 
 @dataclass

@@ -111,3 +111,19 @@ def test_prf_scores_match_sklearn():
         want = (precision_score(y, p, average=avg, zero_division=0), recall_score(y, p, average=avg, zero_division=0),
                 f1_score(y, p, average=avg, zero_division=0))
         assert np.allclose(s[avg], want, atol=1e-9), avg
+
+
+def test_partition_functions_return_subset_like_objects(monkeypatch):
+    monkeypatch.setenv("LDNN_SYNTHETIC", "1")
+    from ldnn_b200 import compat, data as D
+    b = D.make_synthetic(400, 50, 50)
+    sub, idx = compat.get_dataset_partition(b.trainset, 1, [0.25] * 4)
+    assert len(sub) == 100 == len(idx) and list(sub.indices) == list(range(100, 200))
+    x, y = sub[3]
+    assert x.shape == (3, 32, 32) and y == int(b.trainset.labels[103])
+    sub2, idx2, fixed = compat.get_dataset_partition(b.trainset, 1, [0.25] * 4, 0.5)
+    assert fixed == [2, 3] and len(sub2) == len(idx2)
+    sub3, idx3 = compat.get_next_dataset_partition(b.trainset, idx, 0.5, 0.5, 1.0, torch.tensor([4.0]))
+    assert len(sub3) == 100 and len(idx3) == 100
+    ld = D.Loader(sub3, None, 32)                      # a SubsetView is loadable like a dataset
+    assert sum(len(yy) for _, yy in ld) == 100
