@@ -7,6 +7,8 @@ activations NHWC bf16, conv weights KRSC bf16 (``[Cout][R*S*Cin]``), statistics 
 from __future__ import annotations
 
 import ctypes as C
+import json
+import os
 from typing import Optional
 
 import torch
@@ -76,6 +78,55 @@ class ConvPlan:
 # per-shape autotuning of (block_n, splits): these layers are latency/fill-rate bound, so the best
 # tiling depends on how many CTAs it yields — measured once per shape at plan-build time.
 _TUNE_CACHE = {}
+_TUNE_FILE_LOADED = False
+
+
+def _tune_file():
+    """`LDNN_TUNE_CACHE=<path>`: tuned configs persist across processes (json; one entry per
+    (mode, geometry)).  Lets a production launch skip the timing runs, and lets a profiler run
+    (where event timing would mis-tune) replay the choices of an earlier plain run."""
+    return os.environ.get("LDNN_TUNE_CACHE") or None
+
+
+def _tune_key_str(key):
+    return ",".join(str(int(v)) for v in key)
+
+
+def load_tune_cache(path=None):
+    """Merge a saved tuning file into the in-process cache; returns the number of entries read."""
+    path = path or _tune_file()
+    if not path or not os.path.exists(path):
+        return 0
+    try:
+        with open(path) as f:
+            blob = json.load(f)
+    except (OSError, ValueError):
+        return 0
+    n = 0
+    for ks, cfg in blob.get("configs", {}).items():
+        try:
+            key = tuple(int(v) for v in ks.split(","))
+            _TUNE_CACHE.setdefault(key, (int(cfg[0]), int(cfg[1]), bool(cfg[2])))
+            n += 1
+        except (ValueError, IndexError, TypeError):
+            continue
+    return n
+
+
+def save_tune_cache(path=None):
+    """Write the in-process cache (atomically: several ranks may tune the same shapes at once)."""
+    path = path or _tune_file()
+    if not path:
+        return False
+    blob = {"version": 1, "configs": {_tune_key_str(k): [c[0], c[1], bool(c[2])] for k, c in sorted(_TUNE_CACHE.items())}}
+    tmp = f"{path}.{os.getpid()}.tmp"
+    try:
+        with open(tmp, "w") as f:
+            json.dump(blob, f, indent=0)
+        os.replace(tmp, path)
+    except OSError:
+        return False
+    return True
 
 
 def _time_plan(plan, iters=20, reps=3):
@@ -108,9 +159,13 @@ def tuned_conv_config(mode, geo, make_plan, enabled=True):
     """Returns (block_n, splits, lite) — (0, 0, False) = library heuristics.  `make_plan(block_n,
     splits, lite)` must build a runnable plan (private scratch) for timing.  `lite` (two CTAs per SM)
     is tried only for grids of more than one wave."""
-    if not enabled:
-        return 0, 0, False
-    key = (mode,) + tuple(geo)
+    global _TUNE_FILE_LOADED
+    key = (int(mode),) + tuple(int(v) for v in geo)
+    if not _TUNE_FILE_LOADED:
+        _TUNE_FILE_LOADED = True
+        load_tune_cache()
+    if not enabled:                                # no timing runs; a tuning file, if given, is still replayed
+        return _TUNE_CACHE[key] if (_tune_file() and key in _TUNE_CACHE) else (0, 0, False)
     if key in _TUNE_CACHE:
         return _TUNE_CACHE[key]
     N, H, W, Cin, Cout, R, stride, pad = geo
@@ -134,6 +189,7 @@ def tuned_conv_config(mode, geo, make_plan, enabled=True):
             if t < best_t * 0.95:                  # only leave the heuristic for a clear win
                 best_cfg, best_t = (bn, sp, lite), t
     _TUNE_CACHE[key] = best_cfg
+    save_tune_cache()
     return best_cfg
 
 

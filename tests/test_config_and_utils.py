@@ -77,3 +77,30 @@ def test_rasteriser_writes_valid_png(tmp_path):
             i = raw.index(b"IDAT")
             n = struct.unpack(">I", raw[i - 4:i])[0]
             assert len(zlib.decompress(raw[i + 4:i + 4 + n])) == h * (1 + 3 * w)
+
+
+def test_tune_cache_roundtrip_and_replay(tmp_path, monkeypatch):
+    """Persistent conv-tuning file: written atomically, merged on load, replayed when timing is disabled."""
+    from ldnn_b200.ops import native_ops as K
+    path = tmp_path / "tune.json"
+    monkeypatch.setenv("LDNN_TUNE_CACHE", str(path))
+    monkeypatch.setattr(K, "_TUNE_CACHE", {})
+    monkeypatch.setattr(K, "_TUNE_FILE_LOADED", False)
+    geo = (64, 32, 32, 64, 128, 3, 1, 1)
+    K._TUNE_CACHE[(K.FPROP,) + geo] = (128, 2, True)
+    K._TUNE_CACHE[(K.WGRAD,) + geo] = (0, 0, False)
+    assert K.save_tune_cache()
+    monkeypatch.setattr(K, "_TUNE_CACHE", {})
+    assert K.load_tune_cache() == 2
+    assert K._TUNE_CACHE[(K.FPROP,) + geo] == (128, 2, True)
+    # timing disabled + file given: cached choice is replayed, unknown shapes fall back to heuristics;
+    # make_plan must never be called on this path (no GPU here)
+    boom = lambda *a: (_ for _ in ()).throw(AssertionError("timed"))
+    assert K.tuned_conv_config(K.FPROP, geo, boom, enabled=False) == (128, 2, True)
+    assert K.tuned_conv_config(K.DGRAD, geo, boom, enabled=False) == (0, 0, False)
+    # without a file, disabled means heuristics even if the process cache has an entry
+    monkeypatch.delenv("LDNN_TUNE_CACHE")
+    assert K.tuned_conv_config(K.FPROP, geo, boom, enabled=False) == (0, 0, False)
+    # a corrupt file is ignored
+    path.write_text("{not json")
+    assert K.load_tune_cache(str(path)) == 0
