@@ -46,6 +46,11 @@ def parse():
     p.add_argument("--engine", choices=["native", "torch"], default="native")
     p.add_argument("--no_overlap", action="store_true", help="--sync step: exchange after backward instead of per bucket")
     p.add_argument("--comm_blocks", type=int, default=0)
+    p.add_argument("--shard_ratios", type=float, nargs="+", default=None,
+                   help="Disbalanced variants: per-rank shard sizes (e.g. 4 2 1 1).  --sync global_epoch: rank r runs "
+                        "K*ratio_r/max(ratio) steps before the one exchange; --sync step: every rank steps K times "
+                        "with per-rank batch = batch*ratio_r/max(ratio)")
+    p.add_argument("--aggregation_type", choices=["equal", "weighted", "shard"], default="equal")
     return p.parse_args()
 
 
@@ -74,11 +79,25 @@ def run_ours(a):
     cfg = resolve(Config(topology=a.topology, sync=a.sync, model=a.model, batch_size=a.batch, backend="nccl",
                          engine=a.engine, exchange_impl=a.exchange_impl, synthetic=True, quiet=True, seed=0,
                          aggregation_by="gradients", semantics="allreduce", apply_exchanged_grads=None,
-                         comm_blocks=a.comm_blocks))
+                         comm_blocks=a.comm_blocks, aggregation_type=a.aggregation_type))
     rt = init_runtime("nccl", seed=0)
     dev = rt.device
+    # Disbalanced shards: each rank's share of the work follows its ratio (the reference's uneven
+    # random_split, Disbalanced */dataloader.py) and the exchange is weighted by n_r / sum(n).
+    ratios = [1.0] * world
+    if a.shard_ratios:
+        if len(a.shard_ratios) != world:
+            raise SystemExit(f"--shard_ratios needs {world} values")
+        ratios = [float(v) for v in a.shard_ratios]
+    share = ratios[rank] / max(ratios)
+    my_steps = a.steps if a.sync == "step" else max(1, round(a.steps * share))
+    if a.sync == "step" and a.shard_ratios:
+        a.batch = max(1, round(a.batch * share))                # per-rank batch; every rank steps K times
+    cfg.batch_size = a.batch
     engine = make_engine(cfg, rt)
     ex = make_exchanger(cfg, rt, engine)
+    if a.aggregation_type == "shard":
+        ex.set_shard_weights([v / sum(ratios) for v in ratios])
     ex.broadcast_state(engine)
     hw = engine.spec.in_hw
     ncls = engine.spec.head().num_classes
@@ -121,7 +140,7 @@ def run_ours(a):
     barrier_sync(dev)
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
-    epoch(a.steps)
+    epoch(my_steps)
     t1.record()
     barrier_sync(dev)
     ms = t0.elapsed_time(t1)
@@ -157,22 +176,27 @@ def run_ours(a):
     e2e_epoch(3)
     barrier_sync(dev)
     w0 = time.perf_counter()
-    e2e_epoch(a.steps)
+    e2e_epoch(my_steps)
     barrier_sync(dev)
     e2e_s = max_over_ranks(time.perf_counter() - w0, dev)
     clk.__exit__(None, None, None)
 
     if hasattr(ex, "check"):
         ex.check()
-    samples = a.batch * a.steps * world
+    samples = a.batch * my_steps                               # this rank's; summed over ranks below
+    if world > 1:
+        t = torch.tensor([float(samples)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t)
+        samples = float(t[0])
     out = {
         "metric": METRIC if a.model == "enhanced_cnn" else METRIC.replace("EnhancedCNN, batch 64/GPU", f"ResNet-50 @{hw}, batch {a.batch}/GPU"),
         "value": samples / (ms / 1e3), "unit": "samples/s", "n_gpus": world, "steps": a.steps,
         "warmup": max(a.warmup, 3), "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16" if a.engine == "native" else "fp32", "data": "synthetic", "impl": "ours",
-        "config": {"model": a.model, "global_batch": a.batch * world, "per_gpu_batch": a.batch,
+        "config": {"model": a.model, "global_batch": int(round(samples / a.steps)), "per_gpu_batch": a.batch,
                    "input": [3, hw, hw], "optimizer": "adam", "parallelism": f"dp{world}", "topology": a.topology,
                    "sync": a.sync, "overlap": bool(overlap), "exchange": a.exchange_impl, "engine": a.engine,
+                   "aggregation_type": a.aggregation_type, "shard_ratios": a.shard_ratios,
                    "l2": "per-step working set (params+moments+grads ~0.9 GB) and a 16-batch input pool exceed the 126 MB L2"},
         "clocks": clk.summary(),
         "e2e": {"value": samples / e2e_s, "unit": "samples/s",
