@@ -81,3 +81,20 @@ def test_loader_and_sharding_on_cifar_bundle(fake_cifar):
         assert x.shape[1:] == (3, 32, 32)
         seen += len(y)
     assert seen == 40
+
+
+def test_cli_trains_on_disk_dataset_single_process(fake_cifar, tmp_path, monkeypatch):
+    """Whole program on the real-data path (no --synthetic): uint8 images, AutoAugment, dataset
+    statistics, 80/20 split, world_size 1 (exchange is the identity)."""
+    monkeypatch.setenv("LDNN_TINY_WIDTHS", "1")
+    monkeypatch.setenv("MASTER_ADDR", "127.0.0.1")
+    monkeypatch.setenv("MASTER_PORT", str(29900 + os.getpid() % 90))
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    from ldnn_b200 import cli
+    out = tmp_path / "graphs"
+    h = cli.main(["--backend", "gloo", "--data_root", fake_cifar, "--epochs_global", "2", "--epochs_local", "1",
+                  "--batch_size", "16", "--output_folder", str(out), "--quiet", "--seed", "5"],
+                 topology="allreduce", balance="balanced")
+    assert len(h.global_train_losses) == 2 and all(np.isfinite(h.global_train_losses))
+    assert os.path.exists(out / "training_metrics.png") and os.path.exists(out / "metrics.json")
