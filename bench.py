@@ -149,26 +149,36 @@ def run_ours(a):
 
     # ---- end to end through the public API: pinned H2D of every batch, D2H of every loss ----
     copy_stream = torch.cuda.Stream(dev)
-    host_loss = torch.zeros(1).pin_memory()
+    host_loss = torch.zeros(2).pin_memory()
 
     def e2e_epoch(k):
+        """Every step: H2D of its batch from pinned memory (prefetched one step ahead on a copy stream) and a
+        D2H of its loss into pinned memory.  The host reads the loss of step i-1 after it has queued step i
+        (how a logging trainer runs), so the launch of the next step is not held back by the read; all k
+        losses are on the host before the region ends."""
         tot = 0.0
-        nxt = None
+        cur = torch.cuda.current_stream()
+        done = [None, None]
         with torch.cuda.stream(copy_stream):
             nxt = (xs_pin[0].to(dev, non_blocking=True), ys_pin[0].to(dev, non_blocking=True))
             ev = torch.cuda.Event(); ev.record(copy_stream)
         for i in range(k):
-            torch.cuda.current_stream().wait_event(ev)
+            cur.wait_event(ev)
             x, y = nxt
+            x.record_stream(cur); y.record_stream(cur)      # allocated on the copy stream, consumed here
             if i + 1 < k:
                 with torch.cuda.stream(copy_stream):
                     j = (i + 1) % pool
                     nxt = (xs_pin[j].to(dev, non_blocking=True), ys_pin[j].to(dev, non_blocking=True))
                     ev = torch.cuda.Event(); ev.record(copy_stream)
             loss = step(i, x, y)
-            host_loss.copy_(loss.detach().view(1), non_blocking=True)
-            torch.cuda.current_stream().synchronize()      # the step's loss is on the host
-            tot += float(host_loss[0])
+            host_loss[i & 1:(i & 1) + 1].copy_(loss.detach().view(1), non_blocking=True)
+            done[i & 1] = torch.cuda.Event(); done[i & 1].record(cur)
+            if i > 0:
+                done[(i - 1) & 1].synchronize()            # step i-1's loss is on the host
+                tot += float(host_loss[(i - 1) & 1])
+        done[(k - 1) & 1].synchronize()
+        tot += float(host_loss[(k - 1) & 1])
         if not sync_step:
             ex.exchange_grads(engine, apply_update=False)
         return tot
