@@ -184,6 +184,79 @@ allreduce_fused_kernel(const ldnn_comm c, const ldnn_exchange e) {
   }
 }
 
+// ================================================================== K-AR (NVLS): reduce in the switch
+// Same ownership and tails as the two-shot kernel, but the reduce-scatter leg is ONE multimem.ld_reduce per
+// 16 bytes on the multicast mapping of the slab (NVSwitch adds the W copies and returns the sum) and the
+// all-gather leg is ONE multimem.st (the switch replicates the store to every rank).  Per GPU and direction
+// that is ~S bytes on the links instead of 2*S*(W-1)/W.  The per-rank weight must be uniform (the switch can
+// only add); the scale is applied to the sum.  MC=false is the same control flow with the multimem
+// instructions spelled out as W peer loads / W peer stores: it runs in the single-GPU emulation (tests).
+// Staged: compiled and wired (LDNN_NVLS=1), not yet measured on hardware — see DESIGN.md.
+__device__ __forceinline__ float4 mm_ld_reduce_f4(const float4* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mm_st_f4(float4* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w) : "memory");
+}
+
+template <bool MC>
+__global__ void __launch_bounds__(kCommThreads, 1)
+allreduce_nvls_kernel(const ldnn_comm c, const ldnn_exchange e, float4* const mc_data, float4* const mc_params,
+                      const float scale) {
+  const Ctx x = make_ctx(c);
+  const int W = x.world, r = x.rank;
+  const long long n4 = e.n >> 2;
+  const long long per = (n4 + W - 1) / W;
+  const long long lo = min((long long)r * per, n4), hi = min(lo + per, n4);
+  const unsigned int seq = c.epoch * 4u;
+  const bool update = (e.mode & LDNN_X_UPDATE) != 0;
+
+  comm_barrier(x, seq + 1);   // every rank's input slab is final
+
+  float4* const my_params = reinterpret_cast<float4*>(e.params[r]);
+  float4* const my_m = reinterpret_cast<float4*>(e.m);
+  float4* const my_v = reinterpret_cast<float4*>(e.v);
+  const long long stride = (long long)x.blocks * kCommThreads;
+  for (long long i = lo + (long long)x.block * kCommThreads + threadIdx.x; i < hi; i += stride) {
+    float4 s;
+    if (MC) {
+      s = mm_ld_reduce_f4(mc_data + i);
+    } else {
+      s = make_float4(0, 0, 0, 0);
+#pragma unroll
+      for (int p = 0; p < LDNN_MAX_RANKS; ++p)
+        if (p < W) s = f4_fma(ld_sys_f4(reinterpret_cast<const float4*>(e.grads[p]) + i), 1.f, s);
+    }
+    s = f4_scale(s, scale);
+    if (update) {
+      float4 p0 = my_params[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
+      optim_update4(p0, s, m0, v0, e.opt);
+      my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
+      s = p0;
+    }
+    if (MC) {
+      mm_st_f4((update ? mc_params : mc_data) + i, s);
+    } else {
+#pragma unroll
+      for (int q = 0; q < LDNN_MAX_RANKS; ++q)
+        if (q < W) st_sys_f4(reinterpret_cast<float4*>(update ? e.params[q] : e.grads[q]) + i, s);
+    }
+  }
+
+  comm_barrier(x, seq + 2);   // every owner's multicast stores have landed everywhere
+
+  const bool cast = e.shadow != nullptr && (update || (e.mode & 4));
+  if (cast) {
+    const float4* src = update ? my_params : reinterpret_cast<const float4*>(e.grads[r]);
+    __nv_bfloat16* sh = reinterpret_cast<__nv_bfloat16*>(e.shadow);
+    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n4; i += stride) store_bf16x4(sh + 4 * i, src[i]);
+  }
+}
+
 // ================================================================== K-RING / K-DRING: RS + AG rings
 // Region k of the slab belongs to ring k; ring 0 rotates +1 (sends to r+1), ring 1 rotates -1.
 // PUSH design: every hop is local loads -> remote *stores* into the next rank's buffer, followed by a
@@ -427,6 +500,24 @@ extern "C" int ldnn_allreduce_fused(const ldnn_comm* c, const ldnn_exchange* x, 
   LDNN_ARG(x->n % 4 == 0, "allreduce: n=%lld must be a multiple of 4", x->n);
   LDNN_ARG(!(x->mode & LDNN_X_UPDATE) || (x->m && (x->opt.kind == 1 || x->v)), "allreduce: UPDATE needs m (and v)");
   return launch_comm(allreduce_fused_kernel, *c, (cudaStream_t)stream, *c, *x);
+}
+
+extern "C" int ldnn_allreduce_nvls(const ldnn_comm* c, const ldnn_exchange* x, void* mc_data, void* mc_params,
+                                   void* stream) {
+  LDNN_ARG(x->n % 4 == 0, "nvls allreduce: n=%lld must be a multiple of 4", x->n);
+  LDNN_ARG(!(x->mode & LDNN_X_SELFMIX), "nvls allreduce: self-weighted mixing needs the two-shot kernel");
+  LDNN_ARG(!(x->mode & LDNN_X_UPDATE) || (x->m && (x->opt.kind == 1 || x->v)), "nvls allreduce: UPDATE needs m (and v)");
+  for (int p = 1; p < c->world; ++p)
+    LDNN_ARG(x->weight[p] == x->weight[0], "nvls allreduce: per-rank weights must be uniform (rank %d: %g vs %g)", p,
+             (double)x->weight[p], (double)x->weight[0]);
+  const bool mc = !c->emulate;
+  LDNN_ARG(!mc || (mc_data && (!(x->mode & LDNN_X_UPDATE) || mc_params)), "nvls allreduce: multicast mapping missing");
+  LDNN_ARG(!mc || (((uintptr_t)mc_data | (uintptr_t)mc_params) & 15) == 0, "nvls allreduce: multicast pointers must be 16-byte aligned");
+  if (mc)
+    return launch_comm(allreduce_nvls_kernel<true>, *c, (cudaStream_t)stream, *c, *x, (float4*)mc_data, (float4*)mc_params,
+                       x->weight[0]);
+  return launch_comm(allreduce_nvls_kernel<false>, *c, (cudaStream_t)stream, *c, *x, (float4*)nullptr, (float4*)nullptr,
+                     x->weight[0]);
 }
 
 extern "C" int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int num_rings, void* stream) {

@@ -196,6 +196,12 @@ typedef struct {
 
 /* K-AR: two-shot all-reduce (pull-reduce owned slice, fused tail, push to peers) */
 int ldnn_allreduce_fused(const ldnn_comm* c, const ldnn_exchange* x, void* stream);
+/* K-AR (NVLS): the same exchange with the reduce done inside NVSwitch: `mc_data` / `mc_params` are the MULTICAST
+ * mappings (one address = the same offset of every rank's slab) of x->grads / x->params, offset like them.
+ * multimem.ld_reduce on the owned slice, fused tail, multimem.st to all ranks.  Weights must be uniform, SELFMIX
+ * is not available.  With c->emulate the multimem instructions are replaced by peer loads/stores (mc_* ignored).
+ * Staged in round 1: opt-in (LDNN_NVLS=1), not yet measured on hardware. */
+int ldnn_allreduce_nvls(const ldnn_comm* c, const ldnn_exchange* x, void* mc_data, void* mc_params, void* stream);
 /* K-RING / K-DRING: reduce-scatter + all-gather around 1 or 2 (counter-rotating) rings */
 int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int num_rings, void* stream);
 /* compat gossip: out = c_self*x + sum_d c_d * x[(r-d) mod ws], d in offsets (1 or 2 entries) */

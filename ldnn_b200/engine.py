@@ -201,10 +201,17 @@ class TorchEngine(Engine):
         from .ops import native_ops as K
 
         def alloc(n):
-            t, handle, ptr = K.symm_alloc(n * 4, self.device)
-            self._symm[["params", "grads", "m", "v"][len(self._symm)]] = (t, handle, ptr)
+            name = ["params", "grads", "m", "v"][len(self._symm)]
+            if name in ("params", "grads") and K.nvls_requested():
+                t, handle, ptr = K.symm_alloc_multicast(n * 4, self.device)      # LDNN_NVLS=1 (staged)
+            else:
+                t, handle, ptr = K.symm_alloc(n * 4, self.device)
+            self._symm[name] = (t, handle, ptr)
             return t.view(torch.float32)
         return alloc
+
+    def symm_tensor(self, name: str) -> torch.Tensor:
+        return self._symm[name][0]
 
     def symm_handle(self, name: str):
         if name not in self._symm:

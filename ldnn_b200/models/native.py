@@ -117,13 +117,19 @@ class NativeEngine(Engine):
 
     # ------------------------------------------------------------------ memory
     def _alloc_flat(self, n: int) -> torch.Tensor:
-        t, handle, ptr = K.symm_alloc(n * 4, self.device)
         name = ["params", "grads", "m", "v"][len(self._symm)]
+        if name in ("params", "grads") and K.nvls_requested():
+            t, handle, ptr = K.symm_alloc_multicast(n * 4, self.device)     # LDNN_NVLS=1 (staged)
+        else:
+            t, handle, ptr = K.symm_alloc(n * 4, self.device)
         self._symm[name] = (t, handle, ptr)
         return t.view(torch.float32)
 
     def symm_handle(self, name: str):
         return self._symm[name][1], self._symm[name][2], self.flat.total * 4
+
+    def symm_tensor(self, name: str) -> torch.Tensor:
+        return self._symm[name][0]
 
     # ------------------------------------------------------------------ state_dict <-> internal layout
     def _to_internal(self, key: str, t: torch.Tensor) -> torch.Tensor:

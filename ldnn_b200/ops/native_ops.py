@@ -328,6 +328,44 @@ def symm_alloc(nbytes: int, device):
     return tensor_from_ptr(p.value, nbytes, torch.uint8, device), bytes(h), p.value
 
 
+def nvls_requested() -> bool:
+    """`LDNN_NVLS=1`: keep the exchanged slabs in multicast-capable symmetric memory and use the in-switch
+    all-reduce (`ldnn_allreduce_nvls`) where its preconditions hold.  Staged in round 1 (opt-in)."""
+    if not os.environ.get("LDNN_NVLS"):
+        return False
+    import torch.distributed as dist
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+
+def symm_alloc_multicast(nbytes: int, device):
+    """Slab from torch's symmetric-memory allocator (driver VMM allocation that can be bound to an NVSwitch
+    multicast object).  The peers' mappings and the multicast address come from the rendezvous in
+    `parallel.fused.SymmetricBuffer`; the handle slot is None.  torch is used for the allocation and the
+    handle exchange only — the kernels that touch the memory are ours."""
+    import torch.distributed._symmetric_memory as symm_mem
+    t = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+    t.zero_()
+    return t, None, t.data_ptr()
+
+
+def symm_rendezvous(t: torch.Tensor):
+    """(peer pointers indexed by rank, multicast pointer or 0) of a `symm_alloc_multicast` slab."""
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm_mem
+    group = dist.group.WORLD
+    try:
+        symm_mem.enable_symm_mem_for_group(group.group_name)        # needed by older torch, harmless otherwise
+    except Exception:
+        pass
+    hdl = symm_mem.rendezvous(t, group)
+    base = list(hdl.buffer_ptrs)
+    off = t.data_ptr() - base[hdl.rank]                             # the tensor may sit inside a larger block
+    if not (0 <= off and off + t.numel() * t.element_size() <= hdl.buffer_size):
+        raise L.LdnnError("symmetric-memory rendezvous returned a block that does not contain the slab")
+    mc = int(hdl.multicast_ptr) if getattr(hdl, "has_multicast_support", False) or hdl.multicast_ptr else 0
+    return [p + off for p in base], (mc + off if mc else 0), hdl
+
+
 def symm_open(handle: bytes, nbytes: int, device):
     p = C.c_void_p(0)
     buf = (C.c_ubyte * 64).from_buffer_copy(handle)

@@ -42,11 +42,19 @@ SM_CLOCK_KHZ = 1_900_000
 class SymmetricBuffer:
     """A local slab + the peers' mappings of the same slab (pointer table indexed by rank)."""
 
-    def __init__(self, name: str, local_ptr: int, handle: bytes, nbytes: int, rt):
+    def __init__(self, name: str, local_ptr: int, handle: Optional[bytes], nbytes: int, rt, tensor=None):
         self.name, self.nbytes = name, nbytes
         self.ptrs: List[int] = [0] * rt.world_size
         self.ptrs[rt.rank] = local_ptr
-        if rt.world_size > 1:
+        self.multicast = 0             # multicast address of the slab (NVLS), 0 = none
+        if handle is None and rt.world_size > 1:
+            # slab from torch's symmetric-memory allocator (LDNN_NVLS=1): peers + multicast from its rendezvous
+            if tensor is None:
+                raise L.LdnnError(f"symmetric slab `{name}` has neither an IPC handle nor a symmetric-memory tensor")
+            self.ptrs, self.multicast, self._hdl = K.symm_rendezvous(tensor)
+            if self.ptrs[rt.rank] != local_ptr:
+                raise L.LdnnError(f"symmetric slab `{name}`: rendezvous pointer mismatch")
+        elif rt.world_size > 1:
             handles: List[Optional[bytes]] = [None] * rt.world_size
             dist.all_gather_object(handles, handle)
             for r, h in enumerate(handles):
@@ -78,7 +86,10 @@ class FusedExchanger:
         self._bufs = {}
         for name in ("params", "grads"):
             h, p, nb = engine.symm_handle(name)
-            self._bufs[name] = SymmetricBuffer(name, p, h, nb, rt)
+            tens = engine.symm_tensor(name) if (h is None and hasattr(engine, "symm_tensor")) else None
+            self._bufs[name] = SymmetricBuffer(name, p, h, nb, rt, tensor=tens)
+        # in-switch reduce (multimem) is used when both slabs have a multicast mapping (LDNN_NVLS=1 + NVSwitch)
+        self.nvls = all(self._bufs[k].multicast for k in ("params", "grads"))
         t, h, p = K.symm_alloc(L.SIGNAL_WORDS * 4, dev)
         self._signal_t = t
         self._bufs["signal"] = SymmetricBuffer("signal", p, h, L.SIGNAL_WORDS * 4, rt)
@@ -140,12 +151,19 @@ class FusedExchanger:
         e.mode = mode
         if opt is not None:
             e.opt = opt
+        # multicast addresses of the same bucket, for the NVLS kernel (python-side attributes, not struct fields)
+        e.mc_data = self._bufs[data].multicast + 4 * lo if self._bufs[data].multicast else 0
+        e.mc_params = self._bufs["params"].multicast + 4 * lo if self._bufs["params"].multicast else 0
+        e.uniform = all(abs(b[i] - b[0]) <= 1e-12 for i in range(self.world))
         return e
 
     def _launch_reduce(self, e: L.Exchange) -> None:
         c = self._comm()
         lib, st = L.lib(), L.stream_ptr()
-        if self.spec.topology == "allreduce" or (e.mode & L.X_SELFMIX):
+        if (self.nvls and self.spec.topology == "allreduce" and not (e.mode & L.X_SELFMIX)
+                and getattr(e, "uniform", False) and getattr(e, "mc_data", 0)):
+            L.check(lib.ldnn_allreduce_nvls(C.byref(c), C.byref(e), C.c_void_p(e.mc_data), C.c_void_p(e.mc_params), st))
+        elif self.spec.topology == "allreduce" or (e.mode & L.X_SELFMIX):
             L.check(lib.ldnn_allreduce_fused(C.byref(c), C.byref(e), st))
         else:
             rings = 1 if self.spec.topology == "ring" else 2

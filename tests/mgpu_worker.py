@@ -80,7 +80,8 @@ def main():
     assert float(eng.flat.params.min()) == 1.0 == float(eng.flat.params.max())
     ex.close()
     if r == 0:
-        print(f"MGPU_OK world={ws} combos={checked}")
+        # LDNN_NVLS=1: the allreduce/equal cases above ran on the in-switch (multimem) kernel when `nvls` is True
+        print(f"MGPU_OK world={ws} combos={checked} nvls={bool(getattr(ex, 'nvls', False))}")
     shutdown(rt)
 
 
