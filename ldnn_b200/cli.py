@@ -50,8 +50,10 @@ def _run(cfg: Config, rt) -> TrainHistory:
         engine.params_changed()
 
     def on_epoch_end(ge, h, sh):
-        if cfg.save and rt.rank == 0:
-            ckpt.save_checkpoint(cfg.save, engine, h, sh, epoch=ge + 1, cfg=cfg)
+        if cfg.save:
+            exchanger.gather_moments(engine)       # collective: fused per-step updates shard the moments by owner
+            if rt.rank == 0:
+                ckpt.save_checkpoint(cfg.save, engine, h, sh, epoch=ge + 1, cfg=cfg)
 
     history = train_global(engine, bundle, shards, cfg, rt, exchanger, history, start_epoch, on_epoch_end)
 

@@ -199,5 +199,10 @@ class DistExchanger:
     def set_shard_weights(self, w) -> None:
         self.spec.shard_weights = list(w)
 
+    def gather_moments(self, engine) -> bool:
+        """Optimizer moments are replicated on this path (every rank runs the whole update): nothing to do.
+        (The fused exchanger shards them — ``FusedExchanger.gather_moments``.)"""
+        return False
+
     def close(self) -> None:
         pass

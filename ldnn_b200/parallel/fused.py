@@ -191,6 +191,7 @@ class FusedExchanger:
         if apply_update:
             f.step += 1
             e = self._exchange_struct("grads", L.X_UPDATE, L.make_optim(f.opt, f.step, f.lr))
+            self._update_buckets = [(0, self.n)]
         else:
             e = self._exchange_struct("grads", 0)
         self._launch_reduce(e)
@@ -203,6 +204,7 @@ class FusedExchanger:
         f = engine.flat
         f.step += 1
         self._step_opt = L.make_optim(f.opt, f.step, f.lr)
+        self._update_buckets = []
         if not hasattr(self, "_comm_stream"):
             self._comm_stream = torch.cuda.Stream(self.rt.device, priority=-1)
 
@@ -217,12 +219,57 @@ class FusedExchanger:
         with torch.cuda.stream(self._comm_stream):
             e = self._exchange_struct("grads", L.X_UPDATE, self._step_opt, lo, hi)
             self._launch_reduce(e)
+        self._update_buckets.append((lo, hi))
 
     def end_step(self, engine) -> None:
         """The next forward needs every bucket's updated parameters."""
         ev = torch.cuda.Event()
         ev.record(self._comm_stream)
         torch.cuda.current_stream(self.rt.device).wait_event(ev)
+
+    def gather_moments(self, engine) -> bool:
+        """Collective, between steps.  The fused tails run the optimizer only on the slice a rank owns, so after
+        per-step fused updates every rank holds current moments for its own slices only (a sharded optimizer
+        state).  Before the state is exported (checkpoint) the slices are put back together on every rank.
+
+        Ownership is not re-derived here: the same kernels are replayed on the same buckets with a probe
+        optimizer (SGD, lr 0, momentum 0: ``m <- g``, parameters unchanged) on an all-ones gradient, which
+        marks exactly the elements this rank updates — for whichever kernel (two-shot, rings, NVLS) and bucket
+        layout the step used.  The marks must tile the slab (checked).  Returns True if a gather ran.
+        Uses ``torch.distributed`` for the two reductions (control plane; checkpoint time only)."""
+        f = engine.flat
+        buckets = list(getattr(self, "_update_buckets", []) or [])
+        if self.world == 1 or not buckets or f.m is None:
+            return False
+        dev = self.rt.device
+        torch.cuda.synchronize(dev)
+        probe = torch.zeros_like(f.m)
+        f.grads.fill_(1.0)                       # the gradient slab is dead between steps
+        opt = L.Optim()
+        opt.kind, opt.lr, opt.momentum, opt.weight_decay, opt.grad_scale = 1, 0.0, 0.0, 0.0, 1.0
+        opt.beta1 = opt.beta2 = opt.eps = 0.0
+        opt.bc1 = opt.bc2 = 1.0
+        for lo, hi in buckets:
+            e = self._exchange_struct("grads", L.X_UPDATE, opt, lo, hi)
+            e.m, e.v, e.shadow = probe.data_ptr() + 4 * lo, 0, 0
+            self._launch_reduce(e)
+        self.check()
+        mine = probe != 0
+        cover = mine.to(torch.float32)
+        dist.all_reduce(cover)
+        f.grads.zero_()
+        self._update_buckets = []
+        if bool((cover == float(self.world)).all()):
+            return False                         # every rank updated everything (self-weighted form): replicated
+        if bool((cover > 1).any()):
+            raise L.LdnnError("moment gather: two ranks claim the same optimizer slice")
+        untouched = cover == 0                   # padding outside every bucket: identical everywhere, keep
+        for t in (f.m, f.v):
+            if t is None:
+                continue
+            t.copy_(torch.where(mine, t, torch.where(untouched, t / self.world, torch.zeros_like(t))))
+            dist.all_reduce(t)
+        return True
 
     def exchange_weights(self, engine) -> None:
         if self.spec.is_gossip():

@@ -70,6 +70,11 @@ def main():
         gathered = [torch.empty_like(eng.flat.params) for _ in range(ws)]
         dist.all_gather(gathered, eng.flat.params)
         assert all(torch.equal(g, gathered[0]) for g in gathered), topo
+        # the fused tail keeps moments only for the slice a rank owns; the gather rebuilds the full state
+        assert ex.gather_moments(eng), topo
+        assert torch.allclose(eng.flat.m, ref.flat.m, atol=1e-6, rtol=1e-3), (topo, "m")
+        assert torch.allclose(eng.flat.v, ref.flat.v, atol=1e-8, rtol=1e-3), (topo, "v")
+        assert not ex.gather_moments(eng)            # nothing sharded since the last gather
         ex.close()
 
     # broadcast
