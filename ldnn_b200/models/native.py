@@ -245,6 +245,8 @@ class NativeEngine(Engine):
     def train_step_sync(self, x, y, exchanger):
         """Product schedule (--sync step): forward/backward with the fused exchange+update of each
         gradient bucket overlapped with the rest of backward (BASELINE north star)."""
+        if getattr(exchanger, "world", 0) == 1:
+            return self.train_step(x, y, update=True)      # no peers: the local bucketed optimizer is the same update
         p = self._plan(int(x.shape[0]), True)
         exchanger.begin_step(self)
         p.run_bucketed(x, y, lambda lo, hi: exchanger.exchange_bucket(self, lo, hi))
