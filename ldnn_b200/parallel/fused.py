@@ -242,7 +242,8 @@ class FusedExchanger:
         if self.world == 1 or not buckets or f.m is None:
             return False
         dev = self.rt.device
-        torch.cuda.synchronize(dev)
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
         probe = torch.zeros_like(f.m)
         f.grads.fill_(1.0)                       # the gradient slab is dead between steps
         opt = L.Optim()
@@ -259,7 +260,7 @@ class FusedExchanger:
         dist.all_reduce(cover)
         f.grads.zero_()
         self._update_buckets = []
-        if bool((cover == float(self.world)).all()):
+        if bool(((cover == float(self.world)) | (cover == 0)).all()):
             return False                         # every rank updated everything (self-weighted form): replicated
         if bool((cover > 1).any()):
             raise L.LdnnError("moment gather: two ranks claim the same optimizer slice")
