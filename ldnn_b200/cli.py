@@ -33,6 +33,7 @@ def run(cfg: Config) -> TrainHistory:
 def _run(cfg: Config, rt) -> TrainHistory:
     engine = make_engine(cfg, rt)
     bundle = D.get_data(cfg, rt.rank)
+    D.place_bundle(bundle, cfg, rt)
     # exchange bring-up first: the broadcast is the first thing that uses it
     exchanger = make_exchanger(cfg, rt, engine, shard_weights=None)
     exchanger.broadcast_state(engine, src=0)

@@ -60,6 +60,9 @@ class Config:
     synthetic_val: int = 1024
     synthetic_test: int = 1024
     data_root: str = "data"
+    augment: str = "batched"                 # batched | per_image | none  (AutoAugment on the on-disk dataset)
+    data_on_device: str = "auto"             # auto (uint8 on-disk dataset on a GPU) | on | off
+    chunk_batches: int = 0                   # batches gathered+augmented per call; 0 = 64 on device, 16 on host
     shard_ratios: Optional[List[float]] = None  # explicit per-rank sizes, e.g. 4 2 1 1
     probe_batches: int = 10
     replace: Optional[bool] = None           # re-shard sampling with replacement (None → variant default)
@@ -118,6 +121,13 @@ def build_parser(topology: Optional[str] = None, balance: Optional[str] = None) 
     p.add_argument("--synthetic_val", type=int, default=d.synthetic_val)
     p.add_argument("--synthetic_test", type=int, default=d.synthetic_test)
     p.add_argument("--data_root", type=str, default=d.data_root)
+    p.add_argument("--augment", type=str, default=d.augment, choices=["batched", "per_image", "none"],
+                   help="AutoAugment on the on-disk dataset: whole batches at once (default), upstream's one image "
+                        "at a time, or off")
+    p.add_argument("--data_on_device", type=str, default=d.data_on_device, choices=["auto", "on", "off"],
+                   help="keep the dataset resident in GPU memory (auto: the uint8 on-disk dataset only)")
+    p.add_argument("--chunk_batches", type=int, default=d.chunk_batches,
+                   help="batches gathered / augmented per call (0 = 64 when resident on the device, else 16)")
     p.add_argument("--shard_ratios", type=float, nargs="+", default=None)
     p.add_argument("--probe_batches", type=int, default=d.probe_batches)
     p.add_argument("--replace", type=lambda s: s.lower() in ("1", "true", "yes"), default=None)

@@ -54,16 +54,34 @@ class ArrayDataset:
         x, y = self.batch(np.asarray([int(i)]))
         return x[0], int(y[0])
 
+    def to(self, device) -> "ArrayDataset":
+        """Keep the images resident on `device` (a CIFAR-10 shard is ~120 MB of uint8 against 180 GB of HBM):
+        batches are then gathered, augmented and normalised on the device and no per-step H2D copy is left."""
+        device = torch.device(device)
+        self.images = self.images.to(device)
+        if self.mean is not None:
+            self.mean, self.std = self.mean.to(device), self.std.to(device)
+        return self
+
+    @property
+    def device(self) -> torch.device:
+        return self.images.device
+
     def batch(self, idx: np.ndarray) -> Tuple[torch.Tensor, torch.Tensor]:
-        it = torch.as_tensor(np.asarray(idx, dtype=np.int64))
+        it = torch.as_tensor(np.asarray(idx, dtype=np.int64)).to(self.images.device)
         x = self.images.index_select(0, it)
         if x.dtype == torch.uint8:
             if self.augment is not None:
-                x = torch.stack([self.augment(im) for im in x])
+                if getattr(self.augment, "batched", False):
+                    x = self.augment(x)                       # whole uint8 batch at once, on the data's device
+                else:
+                    x = torch.stack([self.augment(im) for im in x])
             x = x.float().div_(255.0)
             if self.mean is not None:
                 x = (x - self.mean) / self.std
         y = torch.from_numpy(self.labels[np.asarray(idx, dtype=np.int64)])
+        if x.device.type != "cpu":
+            y = y.to(x.device, non_blocking=True)
         return x, y
 
     def subset_view(self, idx: np.ndarray) -> "ArrayDataset":
@@ -100,6 +118,14 @@ class DataBundle:
     num_classes: int
     source: str
 
+    def to(self, device) -> "DataBundle":
+        for ds in (self.trainset, self.valset, self.testset):
+            ds.to(device)
+        return self
+
+    def nbytes(self) -> int:
+        return sum(ds.images.numel() * ds.images.element_size() for ds in (self.trainset, self.valset, self.testset))
+
 
 def make_synthetic(n_train=4096, n_val=1024, n_test=1024, num_classes=10, hw=32, channels=3,
                    seed=0) -> DataBundle:
@@ -119,10 +145,14 @@ def make_synthetic(n_train=4096, n_val=1024, n_test=1024, num_classes=10, hw=32,
     return DataBundle(draw(n_train, 1), draw(n_val, 2), draw(n_test, 3), num_classes, "synthetic")
 
 
-def load_cifar10(root="data", augment=True, rng: Optional[np.random.Generator] = None) -> DataBundle:
+def load_cifar10(root="data", augment="batched", rng: Optional[np.random.Generator] = None) -> DataBundle:
     """CIFAR-10 with the reference pipeline: dataset mean/std, AutoAugment on the
     training images, 80/20 train/val split (``dataloader.py:10-35``).  Needs the
-    archive on disk (no network here) — callers fall back to synthetic."""
+    archive on disk (no network here) — callers fall back to synthetic.
+
+    ``augment``: "batched" (default; `ops.augment.BatchedAutoAugment`, same pixel math applied to whole
+    batches on the data's device), "per_image" / True (torchvision's transform one image at a time, as
+    upstream), "none" / False."""
     import torchvision
     from torchvision import transforms
     full = torchvision.datasets.CIFAR10(root, train=True, download=False)
@@ -134,7 +164,15 @@ def load_cifar10(root="data", augment=True, rng: Optional[np.random.Generator] =
     n_tr = int(0.8 * len(full))
     imgs = torch.from_numpy(full.data).permute(0, 3, 1, 2).contiguous()
     labels = np.asarray(full.targets, dtype=np.int64)
-    aug = transforms.AutoAugment(transforms.AutoAugmentPolicy.CIFAR10) if augment else None
+    if augment in ("batched",):
+        from .ops.augment import BatchedAutoAugment
+        aug = BatchedAutoAugment("cifar10")
+    elif augment in (True, "per_image"):
+        aug = transforms.AutoAugment(transforms.AutoAugmentPolicy.CIFAR10)
+    elif augment in (False, None, "none"):
+        aug = None
+    else:
+        raise ValueError(f"augment={augment!r}: expected batched | per_image | none")
     train = ArrayDataset(imgs[perm[:n_tr]], labels[perm[:n_tr]], mean, std, aug)
     val = ArrayDataset(imgs[perm[n_tr:]], labels[perm[n_tr:]], mean, std, aug)  # upstream: valset shares the train transform
     timgs = torch.from_numpy(test.data).permute(0, 3, 1, 2).contiguous()
@@ -145,7 +183,7 @@ def load_cifar10(root="data", augment=True, rng: Optional[np.random.Generator] =
 def get_data(cfg, rank=0) -> DataBundle:
     if not cfg.synthetic:
         try:
-            return load_cifar10(cfg.data_root)
+            return load_cifar10(cfg.data_root, augment=getattr(cfg, "augment", "batched"))
         except Exception as e:  # no archive / no torchvision → synthetic, loudly
             if rank == 0 and not cfg.quiet:
                 print(f"[data] CIFAR-10 unavailable ({type(e).__name__}: {e}); using synthetic data")
@@ -153,6 +191,29 @@ def get_data(cfg, rank=0) -> DataBundle:
     hw = 224 if cfg.model == "resnet50" else 32
     return make_synthetic(cfg.synthetic_train, cfg.synthetic_val, cfg.synthetic_test, cfg.num_classes,
                           hw=hw, seed=seed)
+
+
+def place_bundle(bundle: DataBundle, cfg, rt, cap_bytes: int = 16 << 30) -> bool:
+    """Device residency of the dataset (``--data_on_device``): ``auto`` moves the uint8 on-disk dataset onto the
+    rank's GPU (gather + augmentation + normalisation then run there and the per-step H2D copy disappears),
+    ``on`` moves any dataset that fits, ``off`` keeps the pinned double-buffer path.  Returns True if moved."""
+    mode = getattr(cfg, "data_on_device", "auto")
+    if mode == "off" or not getattr(rt, "is_cuda", False) or bundle.nbytes() > cap_bytes:
+        return False
+    if mode == "auto" and bundle.trainset.images.dtype != torch.uint8:
+        return False
+    bundle.to(rt.device)
+    return True
+
+
+def chunk_batches_for(cfg, dataset: ArrayDataset) -> int:
+    """How many batches a Loader gathers per call: only augmented datasets gain from large chunks."""
+    k = int(getattr(cfg, "chunk_batches", 0) or 0)
+    if k > 0:
+        return k
+    if not getattr(dataset.augment, "batched", False):
+        return 1
+    return 64 if dataset.images.device.type == "cuda" else 16
 
 
 # ---------------------------------------------------------------------------
@@ -254,10 +315,13 @@ def normalise_ratios(r: Sequence[float]) -> List[float]:
 class Loader:
     """``shuffle=False``, keeps the last partial batch (``dataloader.py:42,46,49``)."""
 
-    def __init__(self, dataset: ArrayDataset, indices: Optional[np.ndarray], batch_size: int):
+    def __init__(self, dataset: ArrayDataset, indices: Optional[np.ndarray], batch_size: int, chunk_batches: int = 1):
         self.dataset = dataset
         self.indices = np.arange(len(dataset), dtype=np.int64) if indices is None else np.asarray(indices, np.int64)
         self.batch_size = batch_size
+        # gather / augment / normalise `chunk_batches` batches in one call (amortises the grouped augmentation),
+        # then hand them out one by one — same batches, same order
+        self.chunk_batches = max(1, int(chunk_batches))
 
     def __len__(self) -> int:
         return math.ceil(len(self.indices) / self.batch_size)
@@ -266,8 +330,14 @@ class Loader:
         return len(self.indices)
 
     def __iter__(self):
-        for i in range(0, len(self.indices), self.batch_size):
-            yield self.dataset.batch(self.indices[i:i + self.batch_size])
+        bs, span = self.batch_size, self.batch_size * self.chunk_batches
+        for i in range(0, len(self.indices), span):
+            x, y = self.dataset.batch(self.indices[i:i + span])
+            if self.chunk_batches == 1:
+                yield x, y
+                continue
+            for j in range(0, x.shape[0], bs):
+                yield x[j:j + bs], y[j:j + bs]
 
 
 class DeviceFeeder:
@@ -299,6 +369,8 @@ class DeviceFeeder:
     def _stage(self, x, y):
         if not self.cuda:
             return x, y, None
+        if x.device == self.device:                  # dataset resident on the device: nothing to copy
+            return x, y.to(self.device, non_blocking=True), None
         slot = self._slot
         self._slot ^= 1
         if self._done[slot] is not None:

@@ -218,8 +218,10 @@ def train_global(engine, bundle: D.DataBundle, shards: D.ShardState, cfg, rt, ex
     sync_step = cfg.sync == "step"
 
     for ge in range(start_epoch, cfg.epochs_global):
-        train_loader = D.Loader(bundle.trainset, shards.train_indices, cfg.batch_size)
-        val_loader = D.Loader(bundle.valset, shards.val_indices, cfg.batch_size)
+        train_loader = D.Loader(bundle.trainset, shards.train_indices, cfg.batch_size,
+                                D.chunk_batches_for(cfg, bundle.trainset))
+        val_loader = D.Loader(bundle.valset, shards.val_indices, cfg.batch_size,
+                              D.chunk_batches_for(cfg, bundle.valset))
         capacity = g.max_int(len(train_loader))
         steps = capacity if sync_step else None      # common step count for the per-step schedule
         sums = np.zeros(4, dtype=np.float64)         # train loss/acc, val loss/acc over local epochs
