@@ -260,6 +260,8 @@ class FusedExchanger:
         dist.all_reduce(cover)
         f.grads.zero_()
         self._update_buckets = []
+        if not bool((cover > 0).any()):
+            raise L.LdnnError("moment gather: the probe marked nothing although update buckets were recorded")
         if bool(((cover == float(self.world)) | (cover == 0)).all()):
             return False                         # every rank updated everything (self-weighted form): replicated
         if bool((cover > 1).any()):
