@@ -1,0 +1,58 @@
+"""SURVEY §2.3 behaviours reproduced on the reference schedule (2 ranks, gloo, tiny widths):
+B1 — with --aggregation_by gradients the exchange never reaches the weights (no optimizer step follows it);
+     --aggregation_by weights mixes the models;  the product schedule (--sync step) keeps ranks identical;
+B6 — BN running statistics are broadcast once and then drift per rank (the exchange walks parameters only)."""
+import os
+
+import pytest
+import torch
+
+
+def _worker(rank, world, mode, out_dir):
+    os.environ["LDNN_TINY_WIDTHS"] = "1"
+    from ldnn_b200 import data as D
+    from ldnn_b200.config import Config, resolve
+    from ldnn_b200.engine import make_engine
+    from ldnn_b200.launch import init_runtime, shutdown
+    from ldnn_b200.parallel import make_exchanger
+    from ldnn_b200.trainer import train_global
+    kw = dict(backend="gloo", synthetic=True, synthetic_train=128, synthetic_val=32, synthetic_test=32,
+              epochs_global=2, epochs_local=1, batch_size=32, probe_batches=1, seed=11, quiet=True,
+              topology="allreduce", engine="torch", exchange_impl="dist", output_folder=out_dir)
+    if mode == "gradients":
+        kw.update(aggregation_by="gradients")
+    elif mode == "weights":
+        kw.update(aggregation_by="weights")
+    else:
+        kw.update(sync="step")
+    cfg = resolve(Config(**kw))
+    rt = init_runtime("gloo", seed=cfg.seed)
+    engine = make_engine(cfg, rt)
+    bundle = D.get_data(cfg, rt.rank)
+    ex = make_exchanger(cfg, rt, engine)
+    ex.broadcast_state(engine, src=0)
+    p0 = engine.flat.params.clone()
+    shards = D.initial_shards(bundle, cfg, rt, engine)
+    train_global(engine, bundle, shards, cfg, rt, ex)
+    sd = engine.state_dict()
+    torch.save({"params": engine.flat.params.clone(), "p0": p0,
+                "bn_mean": torch.cat([v.flatten().float() for k, v in sd.items() if k.endswith("running_mean")])},
+               os.path.join(out_dir, f"{mode}_{rank}.pt"))
+    ex.close()
+    shutdown(rt)
+
+
+@pytest.mark.parametrize("mode", ["gradients", "weights", "step"])
+def test_b1_b6_what_the_exchange_reaches(dist_runner, tmp_path, mode):
+    dist_runner(_worker, 2, mode, str(tmp_path))
+    a, b = (torch.load(tmp_path / f"{mode}_{r}.pt") for r in range(2))
+    assert torch.equal(a["p0"], b["p0"])                              # rank-0 broadcast at start (C1)
+    assert not torch.equal(a["params"], a["p0"])                      # training moved the weights
+    if mode == "gradients":
+        # B1: the exchanged gradient is never applied -> the ranks' models only ever saw their own shard
+        assert not torch.allclose(a["params"], b["params"], atol=1e-6)
+    else:
+        # weights are averaged after the last global epoch / every step's update uses the same mean gradient
+        assert torch.allclose(a["params"], b["params"], atol=1e-6)
+    # B6: running statistics are per rank in every mode (different shards, never exchanged after the broadcast)
+    assert not torch.allclose(a["bn_mean"], b["bn_mean"], atol=1e-7)
