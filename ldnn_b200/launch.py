@@ -33,6 +33,23 @@ class Runtime:
     def is_cuda(self) -> bool:
         return self.device.type == "cuda"
 
+    def single_node(self) -> bool:
+        """True when every rank of the job runs on this host (one NVSwitch / CUDA-IPC domain): the fused P2P
+        exchange needs that.  Launchers export LOCAL_WORLD_SIZE; otherwise the hostnames are compared once
+        (collective)."""
+        if self.world_size == 1:
+            return True
+        if not hasattr(self, "_single_node"):
+            lws = os.environ.get("LOCAL_WORLD_SIZE")
+            if lws is not None:
+                self._single_node = int(lws) == self.world_size
+            else:
+                import socket
+                names = [None] * self.world_size
+                dist.all_gather_object(names, socket.gethostname())
+                self._single_node = len(set(names)) == 1
+        return self._single_node
+
 
 def init_runtime(backend: str = "gloo", seed=None, force_cpu: bool = False) -> Runtime:
     rank = int(os.environ.get("RANK", "0"))

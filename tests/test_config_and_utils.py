@@ -104,3 +104,27 @@ def test_tune_cache_roundtrip_and_replay(tmp_path, monkeypatch):
     # a corrupt file is ignored
     path.write_text("{not json")
     assert K.load_tune_cache(str(path)) == 0
+
+
+def test_exchange_impl_follows_the_node_topology(monkeypatch):
+    """auto = fused P2P kernels inside one host, torch.distributed when the job spans hosts; an explicit `fused`
+    across hosts is an error, not a hang."""
+    import types
+    import torch
+    from ldnn_b200.launch import Runtime
+    from ldnn_b200.parallel import make_exchanger
+    from ldnn_b200.parallel.exchange import DistExchanger
+    from ldnn_b200.config import Config, resolve
+    rt = Runtime(rank=0, world_size=16, local_rank=0, device=torch.device("cpu"), backend="gloo", owns_group=False)
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "8")
+    assert rt.single_node() is False
+    rt2 = Runtime(rank=0, world_size=8, local_rank=0, device=torch.device("cpu"), backend="gloo", owns_group=False)
+    assert rt2.single_node() is True
+    assert Runtime(0, 1, 0, torch.device("cpu"), "gloo", False).single_node() is True
+    # a CUDA runtime that spans two hosts: auto -> dist, explicit fused -> clear error
+    fake = types.SimpleNamespace(rank=0, world_size=16, is_cuda=True, device=torch.device("cpu"), single_node=lambda: False)
+    ex = make_exchanger(resolve(Config(exchange_impl="auto")), fake, engine=None)
+    assert isinstance(ex, DistExchanger)
+    import pytest
+    with pytest.raises(RuntimeError, match="one host"):
+        make_exchanger(resolve(Config(exchange_impl="fused")), fake, engine=None)
