@@ -87,6 +87,30 @@ class NetSpec:
             n += c
         return n
 
+    def slot_shapes(self) -> dict:
+        """name -> (H, W, C) of every activation slot, by walking the units (shape inference on the IR)."""
+        shp = {"x": (self.in_hw, self.in_hw, self.in_channels)}
+        for u in self.units:
+            if isinstance(u, Head):
+                continue
+            H, W, Cc = shp[u.src]
+            Ho, Wo = (H + 2 * u.pad - u.k) // u.stride + 1, (W + 2 * u.pad - u.k) // u.stride + 1
+            shp[u.dst] = (Ho, Wo, u.cout if isinstance(u, ConvBN) else Cc)
+        return shp
+
+    def forward_flops(self, batch: int = 1) -> int:
+        """Multiply-add FLOPs (2 per MAC) of the convolutions and the classifier for one forward pass; a training
+        step is ~3x (fprop + dgrad + wgrad).  Used for the roofline report."""
+        shp = self.slot_shapes()
+        total = 0
+        for u in self.units:
+            if isinstance(u, ConvBN):
+                Ho, Wo, _ = shp[u.dst]
+                total += 2 * Ho * Wo * u.cout * u.cin * u.k * u.k
+            elif isinstance(u, Head):
+                total += 2 * u.cin * u.num_classes
+        return int(total) * int(batch)
+
     def _ordered_entries(self):
         # torch orders state_dict by module registration; registration follows the
         # order in which prefixes first appear in ``units`` — except that within a

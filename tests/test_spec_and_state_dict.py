@@ -55,3 +55,14 @@ def test_resnet50_layout():
     assert "layer1.0.downsample.0.weight" in m.state_dict()
     y = m(torch.randn(1, 3, 64, 64))
     assert y.shape == (1, 1000)
+
+
+def test_shape_inference_and_flop_count():
+    from ldnn_b200.models import enhanced_cnn_spec, resnet50_spec
+    s = enhanced_cnn_spec()
+    shp = s.slot_shapes()
+    assert shp["x"] == (32, 32, 3) and shp[s.head().src] == (2, 2, 1024)
+    assert s.forward_flops(1) == 1_077_301_248 and s.forward_flops(64) == 64 * s.forward_flops(1)
+    r = resnet50_spec()
+    assert r.slot_shapes()[r.head().src] == (7, 7, 2048)
+    assert abs(r.forward_flops(1) / 2e9 - 4.09) < 0.02            # the usual 4.1 GMACs of ResNet-50 at 224
