@@ -66,3 +66,18 @@ def test_shape_inference_and_flop_count():
     r = resnet50_spec()
     assert r.slot_shapes()[r.head().src] == (7, 7, 2048)
     assert abs(r.forward_flops(1) / 2e9 - 4.09) < 0.02            # the usual 4.1 GMACs of ResNet-50 at 224
+
+
+def test_resnet50_matches_torchvision_layout_and_forward():
+    """M-R50: same 320-entry state_dict (names, shapes, order) and the same function as torchvision's ResNet-50 v1.5."""
+    tvm = pytest.importorskip("torchvision.models")
+    ref = tvm.resnet50(weights=None)
+    ours = ResNet50()
+    rs, os_ = ref.state_dict(), ours.state_dict()
+    assert list(rs.keys()) == list(os_.keys())
+    assert all(rs[k].shape == os_[k].shape for k in rs)
+    ours.load_state_dict(rs)
+    x = torch.randn(2, 3, 64, 64)
+    ref.eval(); ours.eval()
+    with torch.no_grad():
+        assert torch.allclose(ref(x), ours(x), atol=1e-5, rtol=1e-5)
