@@ -47,14 +47,15 @@ def _run(cfg: Config, rt) -> TrainHistory:
     history = TrainHistory()
     start_epoch = 0
     if cfg.resume:
-        start_epoch = ckpt.load_checkpoint(cfg.resume, engine, history, shards)
+        start_epoch = ckpt.load_checkpoint(cfg.resume, engine, history, shards, rank=rt.rank, world_size=rt.world_size)
         engine.params_changed()
 
     def on_epoch_end(ge, h, sh):
         if cfg.save:
             exchanger.gather_moments(engine)       # collective: fused per-step updates shard the moments by owner
+            everyone = ckpt.gather_shards(sh, rt)  # collective: each rank trains on its own shard
             if rt.rank == 0:
-                ckpt.save_checkpoint(cfg.save, engine, h, sh, epoch=ge + 1, cfg=cfg)
+                ckpt.save_checkpoint(cfg.save, engine, h, sh, epoch=ge + 1, cfg=cfg, all_shards=everyone)
 
     history = train_global(engine, bundle, shards, cfg, rt, exchanger, history, start_epoch, on_epoch_end)
 

@@ -17,15 +17,31 @@ import numpy as np
 import torch
 
 
-def save_checkpoint(path: str, engine, history=None, shards=None, epoch: int = 0, cfg=None) -> None:
+def _shard_blob(shards):
+    return {"train": np.asarray(shards.train_indices), "val": np.asarray(shards.val_indices),
+            "ratios": list(shards.ratios), "fixed_classes": shards.fixed_classes}
+
+
+def gather_shards(shards, rt):
+    """Collective: every rank's shard state, as a list indexed by rank (each rank trains on its own shard, so a
+    checkpoint written by rank 0 has to carry all of them).  Returns None for a single process."""
+    if shards is None or rt is None or rt.world_size == 1:
+        return None
+    import torch.distributed as dist
+    out = [None] * rt.world_size
+    dist.all_gather_object(out, _shard_blob(shards))
+    return out
+
+
+def save_checkpoint(path: str, engine, history=None, shards=None, epoch: int = 0, cfg=None, all_shards=None) -> None:
+    """``shards`` is the writer's own shard state; ``all_shards`` (from :func:`gather_shards`) every rank's."""
     blob = {
         "model": {k: v.detach().cpu() for k, v in engine.state_dict().items()},
         "optimizer": engine.optimizer_state_dict(),
         "epoch": int(epoch),
         "history": None if history is None else dict(vars(history)),
-        "indices": None if shards is None else {
-            "train": np.asarray(shards.train_indices), "val": np.asarray(shards.val_indices),
-            "ratios": list(shards.ratios), "fixed_classes": shards.fixed_classes},
+        "indices": None if shards is None else _shard_blob(shards),
+        "indices_per_rank": all_shards,
         "config": None if cfg is None else cfg.to_dict(),
     }
     tmp = path + ".tmp"
@@ -34,9 +50,13 @@ def save_checkpoint(path: str, engine, history=None, shards=None, epoch: int = 0
     os.replace(tmp, path)
 
 
-def load_checkpoint(path: str, engine, history=None, shards=None) -> int:
+def load_checkpoint(path: str, engine, history=None, shards=None, rank: int = 0, world_size: int = 1) -> int:
     """Restores engine (+history, +shards in place when given).  Returns the next
-    global epoch.  Also accepts a bare ``state_dict`` file written by upstream-style code."""
+    global epoch.  Also accepts a bare ``state_dict`` file written by upstream-style code.
+
+    Shards: rank ``r`` takes its own saved shard when the checkpoint carries one per rank for this world size;
+    a single-process checkpoint restores into a single process; otherwise (world size changed) the freshly
+    computed shards are kept — restoring rank 0's shard everywhere would make every rank train on the same data."""
     blob = torch.load(path, map_location="cpu", weights_only=False)
     if "model" not in blob:                      # bare state_dict
         engine.load_state_dict(blob)
@@ -47,8 +67,14 @@ def load_checkpoint(path: str, engine, history=None, shards=None) -> int:
     if history is not None and blob.get("history"):
         for k, v in blob["history"].items():
             setattr(history, k, v)
-    if shards is not None and blob.get("indices"):
-        ix = blob["indices"]
-        shards.train_indices, shards.val_indices = np.asarray(ix["train"]), np.asarray(ix["val"])
-        shards.ratios, shards.fixed_classes = list(ix["ratios"]), ix["fixed_classes"]
+    if shards is not None:
+        per_rank = blob.get("indices_per_rank")
+        ix = None
+        if per_rank is not None and len(per_rank) == world_size:
+            ix = per_rank[rank]
+        elif per_rank is None and world_size == 1 and blob.get("indices"):
+            ix = blob["indices"]
+        if ix is not None:
+            shards.train_indices, shards.val_indices = np.asarray(ix["train"]), np.asarray(ix["val"])
+            shards.ratios, shards.fixed_classes = list(ix["ratios"]), ix["fixed_classes"]
     return int(blob.get("epoch", 0))

@@ -128,3 +128,33 @@ def test_exchange_impl_follows_the_node_topology(monkeypatch):
     import pytest
     with pytest.raises(RuntimeError, match="one host"):
         make_exchanger(resolve(Config(exchange_impl="fused")), fake, engine=None)
+
+
+def test_checkpoint_restores_each_ranks_own_shard(tmp_path):
+    import types
+    import numpy as np
+    from ldnn_b200.data import ShardState
+    from ldnn_b200.engine import OptimConfig, TorchEngine
+    from ldnn_b200.utils.checkpoint import load_checkpoint, save_checkpoint
+    from test_flat_optimizer import tiny_spec
+    eng = TorchEngine(tiny_spec(), "cpu", OptimConfig())
+    mk = lambda lo, hi: ShardState(np.arange(lo, hi), np.arange(lo, lo + 2), [0.75, 0.25], None)
+    blob = lambda st: {"train": st.train_indices, "val": st.val_indices, "ratios": st.ratios, "fixed_classes": None}
+    path = str(tmp_path / "c.pt")
+    save_checkpoint(path, eng, shards=mk(0, 30), epoch=1, all_shards=[blob(mk(0, 30)), blob(mk(30, 40))])
+    for rank, want in ((0, (0, 30)), (1, (30, 40))):
+        st = mk(100, 110)
+        assert load_checkpoint(path, eng, shards=st, rank=rank, world_size=2) == 1
+        assert st.train_indices[0] == want[0] and st.train_indices[-1] == want[1] - 1
+    # the job now has 4 ranks: nobody inherits rank 0's shard, the fresh split is kept
+    st = mk(100, 110)
+    load_checkpoint(path, eng, shards=st, rank=3, world_size=4)
+    assert st.train_indices[0] == 100
+    # single-process checkpoints restore into a single process
+    save_checkpoint(path, eng, shards=mk(5, 9), epoch=2)
+    st = mk(100, 110)
+    load_checkpoint(path, eng, shards=st)
+    assert st.train_indices[0] == 5
+    st = mk(100, 110)
+    load_checkpoint(path, eng, shards=st, rank=1, world_size=2)
+    assert st.train_indices[0] == 100

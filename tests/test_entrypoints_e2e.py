@@ -46,6 +46,8 @@ def test_step_sync_shard_weighted_and_resume(tmp_path):
     assert len(blob["model"]) == 128 and blob["epoch"] == 2
     assert blob["model"]["layer4.1.conv2.weight"].dtype == torch.float32
     assert len(blob["indices"]["train"]) > 0
+    per_rank = blob["indices_per_rank"]                       # every rank's own shard travels with the checkpoint
+    assert len(per_rank) == 2 and len(per_rank[0]["train"]) > 2 * len(per_rank[1]["train"])      # ratios 3:1
     # resume: one more global epoch
     launch("Disbalanced Ring", 2, ["--sync", "step", "--aggregation_type", "shard", "--shard_ratios", "3", "1",
                                     "--resume", str(ck), "--epochs_global", "3"], out)
