@@ -31,7 +31,19 @@ def run(cfg: Config) -> TrainHistory:
 
 
 def _run(cfg: Config, rt) -> TrainHistory:
-    engine = make_engine(cfg, rt)
+    from .utils.timing import TRACE, nvtx_range
+    if cfg.trace:
+        TRACE.enable()
+    try:
+        return _run_traced(cfg, rt, nvtx_range)
+    finally:
+        if cfg.trace:
+            TRACE.dump(cfg.trace, rt.rank)
+
+
+def _run_traced(cfg: Config, rt, phase) -> TrainHistory:
+    with phase("bring-up"):
+        engine = make_engine(cfg, rt)
     bundle = D.get_data(cfg, rt.rank)
     D.place_bundle(bundle, cfg, rt)
     # exchange bring-up first: the broadcast is the first thing that uses it
@@ -61,8 +73,10 @@ def _run(cfg: Config, rt) -> TrainHistory:
 
     if rt.rank == 0:
         test_loader = D.Loader(bundle.testset, None, cfg.batch_size)
-        evaluate(engine, test_loader, rt, bundle.num_classes, verbose=not cfg.quiet)
-        viz.write_all(history, cfg, rank=rt.rank)
+        with phase("test evaluation"):
+            evaluate(engine, test_loader, rt, bundle.num_classes, verbose=not cfg.quiet)
+        with phase("graphs"):
+            viz.write_all(history, cfg, rank=rt.rank)
     exchanger.close()
     return history
 

@@ -12,6 +12,8 @@ accepted so existing launch lines keep working.
 """
 from __future__ import annotations
 
+import os
+
 import argparse
 from dataclasses import dataclass, field, asdict
 from typing import List, Optional
@@ -63,6 +65,7 @@ class Config:
     augment: str = "batched"                 # batched | per_image | none  (AutoAugment on the on-disk dataset)
     data_on_device: str = "auto"             # auto (uint8 on-disk dataset on a GPU) | on | off
     chunk_batches: int = 0                   # batches gathered+augmented per call; 0 = 64 on device, 16 on host
+    trace: Optional[str] = None              # write a Chrome-trace phase timeline to <trace>.rank<r>.json
     shard_ratios: Optional[List[float]] = None  # explicit per-rank sizes, e.g. 4 2 1 1
     probe_batches: int = 10
     replace: Optional[bool] = None           # re-shard sampling with replacement (None → variant default)
@@ -126,6 +129,9 @@ def build_parser(topology: Optional[str] = None, balance: Optional[str] = None) 
                         "at a time, or off")
     p.add_argument("--data_on_device", type=str, default=d.data_on_device, choices=["auto", "on", "off"],
                    help="keep the dataset resident in GPU memory (auto: the uint8 on-disk dataset only)")
+    p.add_argument("--trace", type=str, default=os.environ.get("LDNN_TRACE") or d.trace,
+                   help="write a Chrome-trace timeline of the phases (train / validate / exchange per epoch) to "
+                        "<PATH>.rank<r>.json")
     p.add_argument("--chunk_batches", type=int, default=d.chunk_batches,
                    help="batches gathered / augmented per call (0 = 64 when resident on the device, else 16)")
     p.add_argument("--shard_ratios", type=float, nargs="+", default=None)

@@ -16,17 +16,53 @@ import torch
 import torch.distributed as dist
 
 
+class PhaseTrace:
+    """Host-side phase timeline (train / validate / exchange per epoch) in Chrome-trace format — open the file in
+    chrome://tracing or Perfetto.  `nsys` is not part of this image; the phases that matter end in a device
+    synchronisation (metrics are read back), so host timestamps at this granularity are device-accurate.
+    Enabled by ``--trace PATH`` (one ``PATH.rank<r>.json`` per rank) or ``LDNN_TRACE=PATH``."""
+
+    def __init__(self):
+        self.enabled = False
+        self.events: List[dict] = []
+        self._t0 = time.perf_counter()
+
+    def enable(self) -> None:
+        self.enabled, self.events, self._t0 = True, [], time.perf_counter()
+
+    def add(self, name: str, t0: float, t1: float, cat: str = "phase", **args) -> None:
+        if self.enabled:
+            self.events.append({"name": name, "cat": cat, "ph": "X", "ts": 1e6 * (t0 - self._t0),
+                                "dur": 1e6 * (t1 - t0), "tid": 0, "args": args})
+
+    def dump(self, path: str, rank: int = 0) -> Optional[str]:
+        if not self.enabled:
+            return None
+        import json
+        import os
+        out = f"{path}.rank{rank}.json"
+        os.makedirs(os.path.dirname(os.path.abspath(out)), exist_ok=True)
+        with open(out, "w") as f:
+            json.dump({"traceEvents": [dict(e, pid=rank) for e in self.events], "displayTimeUnit": "ms"}, f)
+        return out
+
+
+TRACE = PhaseTrace()
+
+
 @contextmanager
 def nvtx_range(name: str):
-    """NVTX range around a phase (shows up in nsys/ncu timelines); no-op without CUDA."""
+    """NVTX range around a phase (shows up in nsys/ncu timelines) + an entry in the phase trace when enabled."""
     on = torch.cuda.is_available()
     if on:
         torch.cuda.nvtx.range_push(name)
+    t0 = time.perf_counter()
     try:
         yield
     finally:
         if on:
             torch.cuda.nvtx.range_pop()
+        TRACE.add(name, t0, time.perf_counter())
 
 
 class CudaTimer:

@@ -98,3 +98,21 @@ def test_cli_trains_on_disk_dataset_single_process(fake_cifar, tmp_path, monkeyp
                  topology="allreduce", balance="balanced")
     assert len(h.global_train_losses) == 2 and all(np.isfinite(h.global_train_losses))
     assert os.path.exists(out / "training_metrics.png") and os.path.exists(out / "metrics.json")
+
+
+def test_phase_trace_is_written_in_chrome_format(tmp_path, monkeypatch):
+    import json
+    monkeypatch.setenv("LDNN_TINY_WIDTHS", "1")
+    monkeypatch.setenv("MASTER_ADDR", "127.0.0.1")
+    monkeypatch.setenv("MASTER_PORT", str(29800 + os.getpid() % 90))
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    from ldnn_b200 import cli
+    cli.main(["--backend", "gloo", "--synthetic", "--synthetic_train", "64", "--synthetic_val", "32", "--synthetic_test", "32",
+              "--epochs_global", "2", "--epochs_local", "1", "--batch_size", "32", "--probe_batches", "1", "--quiet",
+              "--output_folder", str(tmp_path / "g"), "--trace", str(tmp_path / "tl")], topology="allreduce", balance="balanced")
+    blob = json.load(open(tmp_path / "tl.rank0.json"))
+    names = [e["name"] for e in blob["traceEvents"]]
+    assert names.count("exchange") == 2 and names.count("validate") == 2 and "bring-up" in names and "graphs" in names
+    assert sum(n.startswith("train g") for n in names) == 2
+    assert all(e["ph"] == "X" and e["dur"] >= 0 and e["pid"] == 0 for e in blob["traceEvents"])
