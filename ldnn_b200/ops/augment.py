@@ -16,6 +16,30 @@ from typing import Dict, List, Optional, Tuple
 import torch
 
 
+def batched_equalize(x: torch.Tensor) -> torch.Tensor:
+    """Histogram equalisation of every (image, channel) plane of a uint8 ``[B, C, H, W]`` tensor at once.
+
+    torchvision's tensor ``equalize`` loops over images and channels in Python with a data-dependent branch per
+    plane (a host synchronisation each on CUDA).  Same integer arithmetic here, vectorised over the B*C planes:
+    ``step = floor((pixels - count of the brightest occupied bin) / 255)``,
+    ``lut[v] = clamp(floor((cumhist[v-1] + floor(step/2)) / step), 0, 255)``, identity where ``step == 0``."""
+    assert x.dtype == torch.uint8 and x.dim() == 4
+    B, Cc, H, W = x.shape
+    planes = B * Cc
+    v = x.reshape(planes, H * W).to(torch.int64)
+    offs = torch.arange(planes, device=x.device, dtype=torch.int64).unsqueeze(1) * 256
+    hist = torch.bincount((v + offs).reshape(-1), minlength=planes * 256).view(planes, 256)
+    occupied = hist != 0
+    last = 255 - occupied.flip(1).to(torch.int64).argmax(dim=1)                    # brightest occupied bin
+    step = (hist.sum(dim=1) - hist.gather(1, last.unsqueeze(1)).squeeze(1)) // 255
+    safe = step.clamp(min=1).unsqueeze(1)
+    lut = (hist.cumsum(dim=1) + (step // 2).unsqueeze(1)) // safe
+    lut = torch.nn.functional.pad(lut, [1, 0])[:, :-1].clamp(0, 255)
+    out = lut.gather(1, v)
+    out = torch.where((step == 0).unsqueeze(1), v, out)
+    return out.to(torch.uint8).view(B, Cc, H, W)
+
+
 class BatchedAutoAugment:
     batched = True            # ArrayDataset.batch() hands the whole uint8 batch over in one call
 
@@ -53,6 +77,9 @@ class BatchedAutoAugment:
         """x: uint8 [N, C, H, W].  Returns a new uint8 tensor; choices as returned by :meth:`sample`."""
         assert x.dtype == torch.uint8 and x.dim() == 4
         out = x.clone()
+        # group membership is decided on the host (a few thousand integers): the device never has to answer
+        # "is this group empty?", so a CUDA batch is augmented without a single data-dependent synchronisation
+        pid, u, sign = pid.cpu(), u.cpu(), sign.cpu()
         space = self._space((x.shape[2], x.shape[3]))
         fill = self.fill
         if isinstance(fill, (int, float)):
@@ -77,9 +104,13 @@ class BatchedAutoAugment:
                     idx = mask.nonzero(as_tuple=True)[0]
                     if idx.numel() == 0:
                         continue
-                    out[idx] = self._apply_op(out[idx], name, m, interpolation=self.interpolation, fill=fill)
+                    idx = idx.to(x.device)
+                    if name == "Equalize":
+                        out[idx] = batched_equalize(out[idx])      # torchvision's version loops per image and channel
+                    else:
+                        out[idx] = self._apply_op(out[idx], name, m, interpolation=self.interpolation, fill=fill)
         return out
 
     def __call__(self, x: torch.Tensor, generator: Optional[torch.Generator] = None) -> torch.Tensor:
-        pid, u, sign = self.sample(x.shape[0], generator, x.device)
+        pid, u, sign = self.sample(x.shape[0], generator, "cpu")
         return self.apply(x, pid, u, sign)

@@ -107,3 +107,19 @@ def test_place_bundle_and_chunk_policy():
     assert D.chunk_batches_for(Config(chunk_batches=5), u8) == 5
     x, y = u8.to("cpu").batch(np.arange(4))
     assert x.shape == (4, 3, 4, 4) and y.shape == (4,)
+
+
+def test_batched_equalize_is_bit_identical_to_torchvision():
+    from torchvision.transforms import functional as F
+    from ldnn_b200.ops.augment import batched_equalize
+    g = torch.Generator().manual_seed(9)
+    x = torch.randint(0, 256, (40, 3, 32, 32), dtype=torch.uint8, generator=g)
+    x[0] = 7                                                       # constant plane: step == 0 -> unchanged
+    x[1, 0] = torch.randint(100, 104, (32, 32), dtype=torch.uint8, generator=g)    # very narrow histogram
+    x[2] = (x[2] // 64) * 64                                       # four levels
+    x[3, 1, :, :16] = 0; x[3, 1, :, 16:] = 255                      # two extreme levels
+    want = torch.stack([F.equalize(im) for im in x])
+    got = batched_equalize(x)
+    assert got.dtype == torch.uint8 and torch.equal(got, want)
+    small = torch.randint(0, 256, (5, 1, 4, 4), dtype=torch.uint8, generator=g)      # fewer pixels than bins
+    assert torch.equal(batched_equalize(small), torch.stack([F.equalize(im) for im in small]))
