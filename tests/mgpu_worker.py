@@ -77,6 +77,25 @@ def main():
         assert not ex.gather_moments(eng)            # nothing sharded since the last gather
         ex.close()
 
+    # stress: ranks arrive at every exchange with a different, random skew (up to ~1 ms of device-side sleep), the
+    # slab is rewritten between calls — flag epochs, write-after-read on the slabs and the staging buffer must hold
+    import numpy as np
+    rng = np.random.default_rng(1234 + r)
+    for topo in ["allreduce", "ring", "double_ring"]:
+        sp = ExchangeSpec(topo, "allreduce", "shard", 0.5, sw, ws)
+        ex = FusedExchanger(sp, rt, eng, comm_blocks=8, watchdog_ms=5000)
+        M = torch.from_numpy(mixing_matrix(sp))
+        for it in range(24):
+            X = all_data(9000 + it)
+            torch.cuda._sleep(int(rng.integers(0, 2_000_000)))
+            eng.flat.grads.copy_(X[r].float(), non_blocking=True)
+            ex.exchange_grads(eng, apply_update=False)
+            got = eng.flat.grads.double().clone()
+            want = (M @ X)[r].to(dev)
+            assert float((got - want).abs().max()) < 1e-5, (topo, it)
+        ex.check()
+        ex.close()
+
     # broadcast
     sp = ExchangeSpec("allreduce", "allreduce", "equal", 0.5, None, ws)
     ex = FusedExchanger(sp, rt, eng, comm_blocks=8, watchdog_ms=5000)
