@@ -187,7 +187,7 @@ def evaluate(engine, loader: D.Loader, rt, num_classes: int = 10, verbose: bool 
     for x, y in D.DeviceFeeder(loader, dev):
         l, _, p = engine.eval_step(x, y)
         loss_sum += l
-        preds.append(p)
+        preds.append(p.clone())              # the native engine hands out a view of its step-static buffer
         labels.append(y)
     preds = torch.cat(preds).cpu().numpy() if preds else np.zeros(0, np.int64)
     labels = torch.cat(labels).cpu().numpy() if labels else np.zeros(0, np.int64)

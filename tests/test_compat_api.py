@@ -127,3 +127,26 @@ def test_partition_functions_return_subset_like_objects(monkeypatch):
     assert len(sub3) == 100 and len(idx3) == 100
     ld = D.Loader(sub3, None, 32)                      # a SubsetView is loadable like a dataset
     assert sum(len(yy) for _, yy in ld) == 100
+
+
+def test_evaluate_copies_predictions_out_of_engine_static_buffers():
+    """The native engine returns a view of its step-static prediction buffer; evaluate() must not alias it."""
+    import types
+    import numpy as np
+    import torch
+    from ldnn_b200 import data as D
+    from ldnn_b200.trainer import evaluate
+
+    class StaticBufEngine:
+        def __init__(self):
+            self.pred = torch.zeros(8, dtype=torch.int64)
+
+        def eval_step(self, x, y):
+            self.pred[: len(y)] = y                          # "predicts" the labels, into the same buffer every step
+            return torch.tensor(0.5), (self.pred[: len(y)] == y).sum(), self.pred[: len(y)]
+
+    labels = np.arange(24) % 10
+    ds = D.ArrayDataset(torch.zeros(24, 3, 4, 4), labels)
+    rt = types.SimpleNamespace(device=torch.device("cpu"), rank=0)
+    loss, acc, preds, got_labels = evaluate(StaticBufEngine(), D.Loader(ds, None, 8), rt, 10, verbose=False)
+    assert np.array_equal(preds, labels) and np.array_equal(got_labels, labels) and acc == 100.0 and loss == 0.5
