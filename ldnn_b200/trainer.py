@@ -103,9 +103,12 @@ class RecordGather:
 # local epoch / validation / evaluation
 # ---------------------------------------------------------------------------
 def train_local_epoch(engine, loader: D.Loader, rt, exchanger=None, sync_step: bool = False,
-                      num_steps: Optional[int] = None):
+                      num_steps: Optional[int] = None, by_weights: bool = False):
     """One pass over the rank's shard (``trainer.py:194-223``).
-    Returns (mean loss, accuracy %, per-batch losses, samples)."""
+    Returns (mean loss, accuracy %, per-batch losses, samples).
+
+    ``sync_step``: exchange every step — the mean gradient feeds the (fused) update, or with ``by_weights``
+    (``--aggregation_by weights``) every rank updates locally and the parameters are averaged after the step."""
     n_steps = len(loader) if num_steps is None else num_steps
     if n_steps == 0:
         engine.scheduler_step()
@@ -118,7 +121,10 @@ def train_local_epoch(engine, loader: D.Loader, rt, exchanger=None, sync_step: b
         for x, y in D.DeviceFeeder(loader, dev):
             if i >= n_steps:
                 break
-            if sync_step and exchanger is not None:
+            if sync_step and exchanger is not None and by_weights:
+                loss, corr = engine.train_step(x, y, update=True)
+                exchanger.exchange_weights(engine)
+            elif sync_step and exchanger is not None:
                 if hasattr(engine, "train_step_sync") and hasattr(exchanger, "exchange_bucket") \
                         and not exchanger.spec.is_gossip():
                     loss, corr = engine.train_step_sync(x, y, exchanger)      # bucketed, overlapped
@@ -232,7 +238,8 @@ def train_global(engine, bundle: D.DataBundle, shards: D.ShardState, cfg, rt, ex
 
         for le in range(cfg.epochs_local):
             with nvtx_range(f"train g{ge} l{le}"):
-                tl, ta, batch_losses, n = train_local_epoch(engine, train_loader, rt, exchanger, sync_step, steps)
+                tl, ta, batch_losses, n = train_local_epoch(engine, train_loader, rt, exchanger, sync_step, steps,
+                                                            by_weights=cfg.aggregation_by == "weights")
             samples += n
             with nvtx_range("validate"):
                 vl, va = validate(engine, val_loader, rt)

@@ -23,6 +23,8 @@ def _worker(rank, world, mode, out_dir):
         kw.update(aggregation_by="gradients")
     elif mode == "weights":
         kw.update(aggregation_by="weights")
+    elif mode == "step_weights":
+        kw.update(sync="step", aggregation_by="weights")
     else:
         kw.update(sync="step")
     cfg = resolve(Config(**kw))
@@ -42,7 +44,7 @@ def _worker(rank, world, mode, out_dir):
     shutdown(rt)
 
 
-@pytest.mark.parametrize("mode", ["gradients", "weights", "step"])
+@pytest.mark.parametrize("mode", ["gradients", "weights", "step", "step_weights"])
 def test_b1_b6_what_the_exchange_reaches(dist_runner, tmp_path, mode):
     dist_runner(_worker, 2, mode, str(tmp_path))
     a, b = (torch.load(tmp_path / f"{mode}_{r}.pt") for r in range(2))
