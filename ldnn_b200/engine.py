@@ -256,11 +256,17 @@ def make_engine(cfg, rt) -> Engine:
         kw["widths"] = (8, 16, 32, 64, 128)      # test-only: same topology, 1/64 of the FLOPs
     spec = get_spec(cfg.model, **kw)
     kind = cfg.engine
+    dtype = getattr(cfg, "dtype", "bf16")
     if kind == "auto":
-        kind = "native" if rt.is_cuda else "torch"
+        # the sm_100a kernels compute in bf16 (fp32 master weights, fp32 accumulation); --dtype fp32 selects
+        # the torch engine (fp32 model on the same flat slabs, same exchange)
+        kind = "native" if (rt.is_cuda and dtype == "bf16") else "torch"
     if kind == "native":
         if not rt.is_cuda:
             raise RuntimeError("--engine native needs a CUDA device (sm_100a)")
+        if dtype != "bf16":
+            raise RuntimeError("--engine native computes in bf16 with fp32 master weights; use --engine torch "
+                               "(or auto) with --dtype fp32")
         from .models.native import NativeEngine
         # rings are latency-bound per launch: fewer, larger buckets for the overlapped per-step exchange
         bucket_mb = 64 if (cfg.sync == "step" and cfg.topology != "allreduce") else 32

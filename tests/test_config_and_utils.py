@@ -158,3 +158,23 @@ def test_checkpoint_restores_each_ranks_own_shard(tmp_path):
     st = mk(100, 110)
     load_checkpoint(path, eng, shards=st, rank=1, world_size=2)
     assert st.train_indices[0] == 100
+
+
+def test_dtype_flag_selects_the_engine():
+    import types
+    import pytest
+    import torch
+    from ldnn_b200.config import Config
+    from ldnn_b200.engine import TorchEngine, make_engine
+    cpu = types.SimpleNamespace(is_cuda=False, device=torch.device("cpu"), world_size=1, rank=0)
+    import os
+    os.environ["LDNN_TINY_WIDTHS"] = "1"
+    try:
+        assert isinstance(make_engine(Config(dtype="fp32"), cpu), TorchEngine)
+        assert isinstance(make_engine(Config(dtype="bf16"), cpu), TorchEngine)          # no GPU: torch engine
+        fake_gpu = types.SimpleNamespace(is_cuda=True, device=torch.device("cpu"), world_size=1, rank=0)
+        assert isinstance(make_engine(Config(dtype="fp32"), fake_gpu), TorchEngine)     # fp32 on a GPU: torch engine
+        with pytest.raises(RuntimeError, match="bf16"):
+            make_engine(Config(dtype="fp32", engine="native"), fake_gpu)
+    finally:
+        del os.environ["LDNN_TINY_WIDTHS"]
