@@ -343,6 +343,11 @@ def symm_alloc_multicast(nbytes: int, device):
     `parallel.fused.SymmetricBuffer`; the handle slot is None.  torch is used for the allocation and the
     handle exchange only — the kernels that touch the memory are ours."""
     import torch.distributed._symmetric_memory as symm_mem
+    try:
+        if symm_mem.get_backend(device) is None:
+            symm_mem.set_backend("CUDA")          # driver VMM + multicast objects (NVSHMEM is not in this image)
+    except Exception:
+        pass
     t = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
     t.zero_()
     return t, None, t.data_ptr()
