@@ -348,7 +348,13 @@ def symm_alloc_multicast(nbytes: int, device):
             symm_mem.set_backend("CUDA")          # driver VMM + multicast objects (NVSHMEM is not in this image)
     except Exception:
         pass
-    t = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+    try:
+        t = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+    except Exception as e:                        # allocator unavailable on this host: plain IPC slab, no multicast
+        import warnings
+        warnings.warn(f"LDNN_NVLS=1 but torch symmetric memory could not allocate ({type(e).__name__}: {e}); "
+                      "falling back to CUDA-IPC slabs (two-shot kernel)")
+        return symm_alloc(nbytes, device)
     t.zero_()
     return t, None, t.data_ptr()
 
