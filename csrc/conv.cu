@@ -82,6 +82,7 @@ struct Launch {
 };
 struct Plan {
   int mode, block_n, cluster = 1, lite = 0;
+  int pair = 0;                             // cluster == 2 run as a cta_group::2 pair (desc.cluster == -2; staged)
   std::vector<Launch> launches;
   void* out;
   const void* addend;
@@ -139,7 +140,9 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   LDNN_ARG(n_total % bn_ == 0, "N=%d not a multiple of block_n=%d", n_total, bn_);
   plan.mode = d.mode; plan.block_n = bn_;
   plan.lite = d.lite ? 1 : 0;
-  plan.cluster = (d.cluster == 2 && d.mode != MODE_WGRAD && bn_ >= 128) ? 2 : 1;
+  plan.cluster = ((d.cluster == 2 || d.cluster == -2) && d.mode != MODE_WGRAD && bn_ >= 128) ? 2 : 1;
+  plan.pair = (d.cluster == -2 && plan.cluster == 2) ? 1 : 0;
+  LDNN_ARG(!(plan.pair && d.lite), "the CTA-pair variant has no lite form");
   plan.out = (d.mode == MODE_FPROP) ? d.y : (d.mode == MODE_DGRAD ? const_cast<void*>(d.x) : d.dw);
   plan.addend = d.addend ? d.addend : plan.out;
   plan.scratch = d.scratch; plan.tickets = d.tickets;
@@ -341,9 +344,9 @@ static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
     attr[na].val.programmaticStreamSerializationAllowed = 1;
     ++na;
   }
-  if (CL > 1) {
+  if (CL > 1 || CL < 0) {
     attr[na].id = cudaLaunchAttributeClusterDimension;
-    attr[na].val.clusterDim.x = CL; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    attr[na].val.clusterDim.x = CL < 0 ? -CL : CL; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
     ++na;
   }
   cfg.attrs = attr; cfg.numAttrs = na;
@@ -364,6 +367,10 @@ template <int MODE>
 static int launch_bn(const Launch& L, const Plan& pl, cudaStream_t st) {
   if (pl.cluster == 2 && MODE != MODE_WGRAD) {      // cluster path: 128/256-wide tiles, full pipeline
     constexpr int M2 = MODE == MODE_WGRAD ? MODE_FPROP : MODE;
+    if (pl.pair) {                                   // cta_group::2 pair (UMMA_M = 256), staged
+      if (pl.block_n == 128) return launch_one<M2, 128, -2, false>(L, pl, st);
+      return launch_one<M2, 256, -2, false>(L, pl, st);
+    }
     if (pl.block_n == 128) return launch_one<M2, 128, 2, false>(L, pl, st);
     return launch_one<M2, 256, 2, false>(L, pl, st);
   }

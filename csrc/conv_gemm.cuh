@@ -100,12 +100,18 @@ struct ConvCfg {
 // multicasts it into both CTAs' shared memory, halving the L2 reads of the operand both need; a smem
 // stage is recycled only when both CTAs' MMAs have drained it (multicast tcgen05.commit).
 // LITE = short pipeline + 4 epilogue warps, two CTAs per SM (large grids of short-K tiles).
+// CL = -2 ("pair", staged — see NEXT.md 1a): the two CTAs of a TPC run ONE tcgen05.mma.cta_group::2 of UMMA_M = 256:
+// each CTA loads its own A box and only ITS HALF of the B tile (no multicast: half the B bytes enter each SM), the
+// leader CTA issues the MMAs for both, each CTA's TMEM receives its own 128 rows and its epilogue is unchanged.
 template <int MODE, int BLOCK_N, int CL, bool LITE>
 __global__ void __launch_bounds__(LITE ? 192 : 320, LITE ? 2 : 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void* __restrict__ out,
                  const void* __restrict__ addend, float* __restrict__ scratch, unsigned int* __restrict__ tickets,
                  float* __restrict__ stats, const BnBwdFuse fuse) {
   using Cfg = ConvCfg<BLOCK_N>;
+  constexpr bool PAIR = CL < 0;                 // cta_group::2 pair
+  constexpr int CLN = CL < 0 ? -CL : CL;        // CTAs per cluster
+  static_assert(!PAIR || (CLN == 2 && MODE != MODE_WGRAD && BLOCK_N >= 128 && !LITE), "pair: fprop/dgrad, N >= 128");
   constexpr int kStages = LITE ? Cfg::kLiteStages : Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -135,18 +141,26 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
   }
   if (warp == 1) {
     if (elect_one()) {
-      for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], CL); }
+      // pair: one multicast commit per phase frees a stage in both CTAs; multicast cluster: one commit per CTA
+      for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], PAIR ? 1 : CLN); }
       mbar_init(tmem_full, 1);
       fence_mbar_init();
     }
     __syncwarp();
-    tmem_alloc<BLOCK_N>(tmem_ptr);
+    if (!PAIR) tmem_alloc<BLOCK_N>(tmem_ptr);
   }
-  tc_fence_before();
-  if (CL > 1) cluster_sync_all(); else __syncthreads();     // peers' barriers exist before anyone signals them
+  if (PAIR) {
+    cluster_sync_all();                          // both CTAs are running and their barriers exist
+    if (warp == 1) tmem_alloc_2sm<BLOCK_N>(tmem_ptr);   // same warp of both CTAs; same column offset in both
+    tc_fence_before();
+    __syncthreads();
+  } else {
+    tc_fence_before();
+    if (CLN > 1) cluster_sync_all(); else __syncthreads();     // peers' barriers exist before anyone signals them
+  }
   tc_fence_after();
-  const uint32_t crank = (CL > 1) ? cluster_ctarank() : 0u;
-  constexpr uint16_t kMcMask = (1u << CL) - 1u;
+  const uint32_t crank = (CLN > 1) ? cluster_ctarank() : 0u;
+  constexpr uint16_t kMcMask = (1u << CLN) - 1u;
   const uint32_t tmem_base = *tmem_ptr;
   // PDL: everything above overlapped the previous kernel's tail; from here on we touch its outputs
   pdl_wait();
@@ -170,17 +184,37 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sA = smem + stage * Cfg::kStageBytes;
         uint8_t* sB = sA + Cfg::kABytes;
-        mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-        if (MODE == MODE_FPROP || MODE == MODE_DGRAD) {
+        if (PAIR) {
+          // both CTAs' boxes (own A + own half of B, each) are credited to the LEADER's barrier; only it arms it
+          if (crank == 0) mbar_expect_tx(&full_bar[stage], 2 * (Cfg::kABytes + Cfg::kBBytes / 2));
+        } else {
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+        }
+        if (PAIR) {
+          const int tap = it / p.kb_per_tap, kb = it - tap * p.kb_per_tap;
+          const TapEntry te = kc.taps[tap];
+          tma_load_4d_2sm(sA, &maps.act[te.map], &full_bar[stage], kb * 64, w0 + te.dw, h0 + te.dh, nn0);
+          if (MODE == MODE_FPROP) {
+            // my BLOCK_N/2 weight rows, at the SAME smem offset in both CTAs (the MMA reads half of B from each)
+            tma_load_2d_2sm(sB, &maps.other, &full_bar[stage], te.wtap * p.red_ch + kb * 64,
+                            n0 + (int)crank * (BLOCK_N / 2));
+          } else {
+#pragma unroll
+            for (int jj = 0; jj < BLOCK_N / 128; ++jj) {       // my half of the 64-wide ci boxes
+              const int j = (int)crank * (BLOCK_N / 128) + jj;
+              tma_load_2d_2sm(sB + jj * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64, kb * 64);
+            }
+          }
+        } else if (MODE == MODE_FPROP || MODE == MODE_DGRAD) {
           const int tap = it / p.kb_per_tap, kb = it - tap * p.kb_per_tap;
           const TapEntry te = kc.taps[tap];
           tma_load_4d(sA, &maps.act[te.map], &full_bar[stage], kb * 64, w0 + te.dw, h0 + te.dh, nn0);
           if (MODE == MODE_FPROP) {
             // weights [Cout rows][taps*Cin cols], K-major: one box of 64 cols x BLOCK_N rows
-            if (CL == 1) {
+            if (CLN == 1) {
               tma_load_2d(sB, &maps.other, &full_bar[stage], te.wtap * p.red_ch + kb * 64, n0);
             } else {          // my half of the rows, delivered to both CTAs
-              constexpr int kHalfRows = BLOCK_N / CL;
+              constexpr int kHalfRows = BLOCK_N / CLN;
               tma_load_2d_mc(sB + crank * kHalfRows * 128, &maps.other, &full_bar[stage],
                              te.wtap * p.red_ch + kb * 64, n0 + (int)crank * kHalfRows, kMcMask);
             }
@@ -188,9 +222,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
             // weights [Cout rows][taps*Cin cols]; B[n=ci, k=co] is MN-major: boxes of 64 ci x 64 co
 #pragma unroll
             for (int j = 0; j < BLOCK_N / 64; ++j) {
-              if (CL == 1)
+              if (CLN == 1)
                 tma_load_2d(sB + j * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64, kb * 64);
-              else if ((j % CL) == (int)crank)      // boxes dealt round-robin to the cluster's CTAs
+              else if ((j % CLN) == (int)crank)      // boxes dealt round-robin to the cluster's CTAs
                 tma_load_2d_mc(sB + j * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64,
                                kb * 64, kMcMask);
             }
@@ -210,12 +244,12 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc_bf16(128, BLOCK_N, MODE == MODE_WGRAD ? 1u : 0u,
+    constexpr uint32_t idesc = make_idesc_bf16(PAIR ? 256 : 128, BLOCK_N, MODE == MODE_WGRAD ? 1u : 0u,
                                                MODE == MODE_FPROP ? 0u : 1u);
     constexpr uint32_t a_kstep = (MODE == MODE_WGRAD) ? 2048u : 32u;
     constexpr uint32_t b_kstep = (MODE == MODE_FPROP) ? 32u : 2048u;
     int stage = 0; uint32_t phase = 0;
-    for (int it = it_begin; it < it_end; ++it) {
+    for (int it = it_begin; it < it_end && !(PAIR && crank != 0); ++it) {      // pair: only the leader issues
       mbar_wait(&full_bar[stage], phase);
       tc_fence_after();
       if (elect_one()) {
@@ -225,11 +259,17 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
         for (int k = 0; k < 4; ++k) {
           const uint64_t da = make_smem_desc_sw128(sA + k * a_kstep, p.a_lbo, p.a_sbo);
           const uint64_t db = make_smem_desc_sw128(sB + k * b_kstep, p.b_lbo, p.b_sbo);
-          umma_bf16(tmem_base, da, db, idesc, (it > it_begin || k > 0) ? 1u : 0u);
+          if (PAIR) umma_bf16_2sm(tmem_base, da, db, idesc, (it > it_begin || k > 0) ? 1u : 0u);
+          else umma_bf16(tmem_base, da, db, idesc, (it > it_begin || k > 0) ? 1u : 0u);
         }
-        if (CL == 1) umma_commit(&empty_bar[stage]);    // frees the smem slot when these MMAs retire
-        else umma_commit_mc(&empty_bar[stage], kMcMask);   // ... in every CTA that multicasts into it
-        if (it == it_end - 1) umma_commit(tmem_full);   // accumulator complete
+        if (PAIR) {
+          umma_commit_2sm_mc(&empty_bar[stage], kMcMask);                   // frees the stage in BOTH CTAs
+          if (it == it_end - 1) umma_commit_2sm_mc(tmem_full, kMcMask);     // both epilogues may start
+        } else {
+          if (CLN == 1) umma_commit(&empty_bar[stage]);    // frees the smem slot when these MMAs retire
+          else umma_commit_mc(&empty_bar[stage], kMcMask);   // ... in every CTA that multicasts into it
+          if (it == it_end - 1) umma_commit(tmem_full);   // accumulator complete
+        }
       }
       __syncwarp();
       if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -454,10 +494,11 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
     tc_fence_before();
   }
 
-  if (CL > 1) cluster_sync_all(); else __syncthreads();     // a peer may still signal my barriers until it is done
+  if (CLN > 1) cluster_sync_all(); else __syncthreads();     // a peer may still signal my barriers until it is done
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<BLOCK_N>(tmem_base);
+    if (PAIR) tmem_dealloc_2sm<BLOCK_N>(tmem_base);
+    else tmem_dealloc<BLOCK_N>(tmem_base);
   }
 }
 

@@ -1,5 +1,7 @@
 """tcgen05 implicit-GEMM conv (fprop / dgrad / wgrad) vs fp32 torch conv, at every shape of the
 repo model plus ResNet-50-style shapes."""
+import os
+
 import pytest
 import torch
 
@@ -130,6 +132,22 @@ def test_cluster_multicast_weights(case, splits):
     from ldnn_b200.ops import native_ops as K
     assert _run(case, K.FPROP, cluster=2, block_n=128, splits=splits) < 1.5e-2
     assert _run(case, K.DGRAD, cluster=2, block_n=128, splits=splits) < 1.5e-2
+
+
+@pytest.mark.skipif(not os.environ.get("LDNN_TEST_PAIR"), reason="staged cta_group::2 variant: not yet run on hardware "
+                    "(set LDNN_TEST_PAIR=1, and run it under `timeout`)")
+@pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (64, 8, 8, 256, 256, 3, 1, 1),
+                                  (64, 16, 16, 128, 256, 3, 2, 1), (8, 14, 14, 256, 256, 3, 1, 1)])
+@pytest.mark.parametrize("block_n", [128, 256])
+@pytest.mark.parametrize("splits", [1, 3])
+def test_cta_pair_umma_m256(case, block_n, splits):
+    """cluster=-2: the two CTAs of a pair run one tcgen05.mma.cta_group::2 (UMMA_M = 256); each loads half of B."""
+    from ldnn_b200.ops import native_ops as K
+    N, H, W, Cin, Cout, R, s, p = case
+    if Cout % block_n == 0:
+        assert _run(case, K.FPROP, cluster=-2, block_n=block_n, splits=splits) < 1.5e-2
+    if Cin % block_n == 0:
+        assert _run(case, K.DGRAD, cluster=-2, block_n=block_n, splits=splits) < 1.5e-2
 
 
 @pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (8, 56, 56, 64, 256, 1, 1, 0), (6, 8, 8, 256, 512, 3, 2, 1)])
