@@ -44,6 +44,9 @@ def parse():
     p.add_argument("--batch", type=int, default=BATCH)
     p.add_argument("--exchange_impl", choices=["fused", "dist"], default="fused")
     p.add_argument("--engine", choices=["native", "torch"], default="native")
+    p.add_argument("--dtype", choices=["tf32", "bf16"], default="tf32",
+                   help="native engine precision: tf32 = fp32 storage + TF32 tensor-core convolutions (what the "
+                        "reference runs: fp32 tensors, torch's default cudnn.allow_tf32); bf16 = bf16 storage/MMA")
     p.add_argument("--no_overlap", action="store_true", help="--sync step: exchange after backward instead of per bucket")
     p.add_argument("--comm_blocks", type=int, default=0)
     p.add_argument("--shard_ratios", type=float, nargs="+", default=None,
@@ -77,7 +80,8 @@ def run_ours(a):
     if world == 1:
         os.environ.setdefault("MASTER_PORT", str(29500 + os.getpid() % 2000))
     cfg = resolve(Config(topology=a.topology, sync=a.sync, model=a.model, batch_size=a.batch, backend="nccl",
-                         engine=a.engine, exchange_impl=a.exchange_impl, synthetic=True, quiet=True, seed=0,
+                         engine=a.engine, dtype=(a.dtype if a.engine == "native" else "fp32"),
+                         exchange_impl=a.exchange_impl, synthetic=True, quiet=True, seed=0,
                          aggregation_by="gradients", semantics="allreduce", apply_exchanged_grads=None,
                          comm_blocks=a.comm_blocks, aggregation_type=a.aggregation_type))
     rt = init_runtime("nccl", seed=0)

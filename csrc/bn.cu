@@ -97,8 +97,9 @@ __device__ __forceinline__ void fold_partials(const float* __restrict__ partial,
 }
 
 // ------------------------------------------------------------------ forward stats
+template <typename T>
 __global__ void __launch_bounds__(kBnThreads)
-bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* __restrict__ partial, unsigned int* ticket, int M, int C,
+bn_stats_kernel(const T* __restrict__ y, float* __restrict__ partial, unsigned int* ticket, int M, int C,
                 int rows_per_chunk, const float* __restrict__ gamma, const float* __restrict__ beta,
                 float* running_mean, float* running_var, long long* nbt, float* save_mean, float* save_invstd,
                 float* scale, float* shift, float eps, float momentum) {
@@ -110,9 +111,8 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* __restrict__ partial
   const int r0 = blockIdx.y * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
 #pragma unroll 4
   for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
-    const uint4 u = *reinterpret_cast<const uint4*>(y + (size_t)r * C + L.c0);
     float f[8];
-    bf16x8_to_float(u, f);
+    load8(y + (size_t)r * C + L.c0, f);
 #pragma unroll
     for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] += f[i] * f[i]; }
   }
@@ -149,17 +149,17 @@ __global__ void bn_eval_coeffs_kernel(const float* gamma, const float* beta, con
 }
 
 // ------------------------------------------------------------------ forward apply
+template <typename T>
 __global__ void __launch_bounds__(256)
-bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
-                const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out, long long total8, int C,
+bn_apply_kernel(const T* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
+                const T* __restrict__ res, T* __restrict__ out, long long total8, int C,
                 int relu) {
   const int c8 = C >> 3;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total8;
        i += (long long)gridDim.x * blockDim.x) {
     const int cg = (int)(i % c8);
-    const uint4 u = reinterpret_cast<const uint4*>(y)[i];
     float f[8];
-    bf16x8_to_float(u, f);
+    load8(y + 8 * (size_t)i, f);
     const float4 s0 = reinterpret_cast<const float4*>(scale)[cg * 2], s1 = reinterpret_cast<const float4*>(scale)[cg * 2 + 1];
     const float4 h0 = reinterpret_cast<const float4*>(shift)[cg * 2], h1 = reinterpret_cast<const float4*>(shift)[cg * 2 + 1];
     const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
@@ -168,7 +168,7 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ s
     for (int k = 0; k < 8; ++k) f[k] = f[k] * sc[k] + sh[k];
     if (res) {
       float r[8];
-      bf16x8_to_float(reinterpret_cast<const uint4*>(res)[i], r);
+      load8(res + 8 * (size_t)i, r);
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] += r[k];
     }
@@ -176,14 +176,15 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ s
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
     }
-    reinterpret_cast<uint4*>(out)[i] = float_to_bf16x8(f);
+    store8(out + 8 * (size_t)i, f);
   }
 }
 
 // ------------------------------------------------------------------ backward reduce
+template <typename T>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
-                     const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+bn_bwd_reduce_kernel(const T* __restrict__ dout, const T* __restrict__ outp,
+                     const T* __restrict__ y, const float* __restrict__ mean,
                      const float* __restrict__ invstd, float* __restrict__ partial, unsigned int* ticket, int M, int C,
                      int rows_per_chunk, int relu, float* dgamma, float* dbeta) {
   extern __shared__ float smem[];
@@ -196,11 +197,11 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16
   for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
     const size_t off = (size_t)r * C + L.c0;
     float g[8], yy[8];
-    bf16x8_to_float(*reinterpret_cast<const uint4*>(dout + off), g);
-    bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), yy);
+    load8(dout + off, g);
+    load8(y + off, yy);
     if (relu) {
       float o[8];
-      bf16x8_to_float(*reinterpret_cast<const uint4*>(outp + off), o);
+      load8(outp + off, o);
 #pragma unroll
       for (int i = 0; i < 8; ++i) g[i] = (o[i] > 0.f) ? g[i] : 0.f;
     }
@@ -217,36 +218,37 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16
 }
 
 // ------------------------------------------------------------------ backward apply
+template <typename T>
 __global__ void __launch_bounds__(256)
-bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
-                    const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+bn_bwd_apply_kernel(const T* __restrict__ dout, const T* __restrict__ outp,
+                    const T* __restrict__ y, const float* __restrict__ mean,
                     const float* __restrict__ invstd, const float* __restrict__ gamma,
                     const float* __restrict__ dgamma, const float* __restrict__ dbeta,
-                    __nv_bfloat16* __restrict__ dy_raw, __nv_bfloat16* __restrict__ dres, long long total8, int C,
+                    T* __restrict__ dy_raw, T* __restrict__ dres, long long total8, int C,
                     int relu, int res_accumulate, float inv_m) {
   const int c8 = C >> 3;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total8;
        i += (long long)gridDim.x * blockDim.x) {
     const int c0 = (int)(i % c8) * 8;
     float g[8], yy[8];
-    bf16x8_to_float(reinterpret_cast<const uint4*>(dout)[i], g);
-    bf16x8_to_float(reinterpret_cast<const uint4*>(y)[i], yy);
+    load8(dout + 8 * (size_t)i, g);
+    load8(y + 8 * (size_t)i, yy);
     if (relu) {
       float o[8];
-      bf16x8_to_float(reinterpret_cast<const uint4*>(outp)[i], o);
+      load8(outp + 8 * (size_t)i, o);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] = (o[k] > 0.f) ? g[k] : 0.f;
     }
     if (dres) {
       if (res_accumulate) {
         float r[8];
-        bf16x8_to_float(reinterpret_cast<const uint4*>(dres)[i], r);
+        load8(dres + 8 * (size_t)i, r);
         float t[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) t[k] = r[k] + g[k];
-        reinterpret_cast<uint4*>(dres)[i] = float_to_bf16x8(t);
+        store8(dres + 8 * (size_t)i, t);
       } else {
-        reinterpret_cast<uint4*>(dres)[i] = float_to_bf16x8(g);
+        store8(dres + 8 * (size_t)i, g);
       }
     }
     float o8[8];
@@ -257,7 +259,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16*
       const float xh = (yy[k] - mean[c]) * is;
       o8[k] = gamma[c] * is * (g[k] - dbeta[c] * inv_m - xh * dgamma[c] * inv_m);
     }
-    reinterpret_cast<uint4*>(dy_raw)[i] = float_to_bf16x8(o8);
+    store8(dy_raw + 8 * (size_t)i, o8);
   }
 }
 
@@ -267,11 +269,12 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16*
 // save_mean/save_invstd and the running statistics), then streams normalize + residual + ReLU.
 // Backward likewise: `reduce` accumulates (sum dy, sum dy*xhat) with red.add (no ticket chain) and
 // `apply` derives dgamma/dbeta + the per-channel coefficients in its prologue.
+template <typename T>
 __global__ void __launch_bounds__(256)
-bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ sums,
+bn_apply_sums_kernel(const T* __restrict__ y, const float* __restrict__ sums,
                      const float* __restrict__ gamma, const float* __restrict__ beta, float* running_mean,
                      float* running_var, long long* nbt, float* save_mean, float* save_invstd,
-                     const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out, int rows_per_chunk,
+                     const T* __restrict__ res, T* __restrict__ out, int rows_per_chunk,
                      int C, int M, int relu, int training, float eps, float momentum) {
   pdl_wait();
   pdl_launch_dependents();
@@ -311,12 +314,12 @@ bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ y, const float* __restric
   for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
     const size_t off = (size_t)r * C + L.c0;
     float f[8];
-    bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), f);
+    load8(y + off, f);
 #pragma unroll
     for (int k = 0; k < 8; ++k) f[k] = f[k] * sc[k] + sh[k];
     if (res) {
       float rr[8];
-      bf16x8_to_float(*reinterpret_cast<const uint4*>(res + off), rr);
+      load8(res + off, rr);
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] += rr[k];
     }
@@ -324,13 +327,14 @@ bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ y, const float* __restric
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
     }
-    *reinterpret_cast<uint4*>(out + off) = float_to_bf16x8(f);
+    store8(out + off, f);
   }
 }
 
+template <typename T>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_reduce_atomic_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
-                            const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+bn_bwd_reduce_atomic_kernel(const T* __restrict__ dout, const T* __restrict__ outp,
+                            const T* __restrict__ y, const float* __restrict__ mean,
                             const float* __restrict__ invstd, float* __restrict__ sums, int M, int C,
                             int rows_per_chunk, int relu) {
   pdl_wait();
@@ -345,11 +349,11 @@ bn_bwd_reduce_atomic_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_b
   for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
     const size_t off = (size_t)r * C + L.c0;
     float g[8], yy[8];
-    bf16x8_to_float(*reinterpret_cast<const uint4*>(dout + off), g);
-    bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), yy);
+    load8(dout + off, g);
+    load8(y + off, yy);
     if (relu) {
       float o[8];
-      bf16x8_to_float(*reinterpret_cast<const uint4*>(outp + off), o);
+      load8(outp + off, o);
 #pragma unroll
       for (int i = 0; i < 8; ++i) g[i] = (o[i] > 0.f) ? g[i] : 0.f;
     }
@@ -371,12 +375,13 @@ bn_bwd_reduce_atomic_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_b
   }
 }
 
+template <typename T>
 __global__ void __launch_bounds__(256)
-bn_bwd_apply_sums_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ outp,
-                         const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
+bn_bwd_apply_sums_kernel(const T* __restrict__ dout, const T* __restrict__ outp,
+                         const T* __restrict__ y, const float* __restrict__ mean,
                          const float* __restrict__ invstd, const float* __restrict__ gamma,
-                         const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy_raw,
-                         __nv_bfloat16* __restrict__ dres, float* dgamma, float* dbeta, int rows_per_chunk, int M,
+                         const float* __restrict__ sums, T* __restrict__ dy_raw,
+                         T* __restrict__ dres, float* dgamma, float* dbeta, int rows_per_chunk, int M,
                          int C, int relu, int res_accumulate, float inv_m) {
   pdl_wait();
   pdl_launch_dependents();
@@ -401,35 +406,36 @@ bn_bwd_apply_sums_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bflo
   for (int r = r0 + L.pl; r < r1; r += kRowLanes) {
     const size_t off = (size_t)r * C + L.c0;
     float g[8], yy[8];
-    bf16x8_to_float(*reinterpret_cast<const uint4*>(dout + off), g);
-    bf16x8_to_float(*reinterpret_cast<const uint4*>(y + off), yy);
+    load8(dout + off, g);
+    load8(y + off, yy);
     if (relu) {
       float o[8];
-      bf16x8_to_float(*reinterpret_cast<const uint4*>(outp + off), o);
+      load8(outp + off, o);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] = (o[k] > 0.f) ? g[k] : 0.f;
     }
     if (dres) {
       if (res_accumulate) {
         float rr[8], t[8];
-        bf16x8_to_float(*reinterpret_cast<const uint4*>(dres + off), rr);
+        load8(dres + off, rr);
 #pragma unroll
         for (int k = 0; k < 8; ++k) t[k] = rr[k] + g[k];
-        *reinterpret_cast<uint4*>(dres + off) = float_to_bf16x8(t);
+        store8(dres + off, t);
       } else {
-        *reinterpret_cast<uint4*>(dres + off) = float_to_bf16x8(g);
+        store8(dres + off, g);
       }
     }
     float o8[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) o8[k] = kk[k] * (g[k] - kb[k] - (yy[k] - mu[k]) * is[k] * kg[k]);
-    *reinterpret_cast<uint4*>(dy_raw + off) = float_to_bf16x8(o8);
+    store8(dy_raw + off, o8);
   }
 }
 
 // ------------------------------------------------------------------ stem im2col (fp32 NCHW -> bf16 rows)
+template <typename T>
 __global__ void __launch_bounds__(256)
-im2col_stem_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col, int N, int C, int H, int W, int R,
+im2col_stem_kernel(const float* __restrict__ x, T* __restrict__ col, int N, int C, int H, int W, int R,
                    int stride, int pad, int P, int Q, int Kpad) {
   pdl_wait();
   pdl_launch_dependents();
@@ -453,7 +459,7 @@ im2col_stem_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col,
       }
       f[j] = v;
     }
-    reinterpret_cast<uint4*>(col)[i] = float_to_bf16x8(f);
+    store8(col + 8 * (size_t)i, f);
   }
 }
 
@@ -461,7 +467,8 @@ im2col_stem_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col,
 // Forward records the window position of the (first) maximum per output element, so backward is a
 // gather: every input pixel looks at the <= ceil(k/stride)^2 windows that cover it and takes the
 // gradient of those whose recorded position is this pixel (same tie-break as torch: first maximum).
-__global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+template <typename T>
+__global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y,
                                    uint8_t* __restrict__ idx, int N, int H, int W, int C, int k, int stride, int pad,
                                    int P, int Q) {
   pdl_wait();
@@ -482,12 +489,12 @@ __global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
         const int h = p * stride - pad + r, w = q * stride - pad + s;
         if (h < 0 || h >= H || w < 0 || w >= W) continue;
         float f[8];
-        bf16x8_to_float(*reinterpret_cast<const uint4*>(x + (((size_t)n * H + h) * W + w) * C + cg * 8), f);
+        load8(x + (((size_t)n * H + h) * W + w) * C + cg * 8, f);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           if (f[j] > m[j]) { m[j] = f[j]; am[j] = (uint8_t)(r * k + s); }
       }
-    reinterpret_cast<uint4*>(y)[i] = float_to_bf16x8(m);
+    store8(y + 8 * (size_t)i, m);
     if (idx) {
       uint2 packed;
       packed.x = am[0] | (am[1] << 8) | (am[2] << 16) | ((uint32_t)am[3] << 24);
@@ -497,8 +504,9 @@ __global__ void maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
   }
 }
 
-__global__ void maxpool_bwd_kernel(const uint8_t* __restrict__ idx, const __nv_bfloat16* __restrict__ dy,
-                                   __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int k, int stride,
+template <typename T>
+__global__ void maxpool_bwd_kernel(const uint8_t* __restrict__ idx, const T* __restrict__ dy,
+                                   T* __restrict__ dx, int N, int H, int W, int C, int k, int stride,
                                    int pad, int P, int Q) {
   pdl_wait();
   pdl_launch_dependents();
@@ -522,14 +530,14 @@ __global__ void maxpool_bwd_kernel(const uint8_t* __restrict__ idx, const __nv_b
         const size_t o = (((size_t)n * P + p) * Q + q) * c8 + cg;
         const uint2 packed = reinterpret_cast<const uint2*>(idx)[o];
         float g[8];
-        bf16x8_to_float(reinterpret_cast<const uint4*>(dy)[o], g);
+        load8(dy + 8 * (size_t)o, g);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const uint32_t a = ((j < 4 ? packed.x : packed.y) >> (8 * (j & 3))) & 0xffu;
           if (a == me) acc[j] += g[j];
         }
       }
-    reinterpret_cast<uint4*>(dx)[i] = float_to_bf16x8(acc);
+    store8(dx + 8 * (size_t)i, acc);
   }
 }
 
@@ -549,7 +557,8 @@ static int grid_for(long long work, int threads, int max_blocks = 148 * 8) {
 using namespace ldnn;
 #define COUNT_LAUNCH() g_launches.fetch_add(1, std::memory_order_relaxed)
 
-extern "C" int ldnn_bn_fwd_stats(const void* y, int M, int C, int chunks, float* partial, unsigned int* ticket,
+template <typename T>
+static int bn_fwd_stats_impl(const void* y, int M, int C, int chunks, float* partial, unsigned int* ticket,
                                  const float* gamma, const float* beta, float* running_mean, float* running_var,
                                  long long* nbt, float* save_mean, float* save_invstd, float* scale, float* shift,
                                  float eps, float momentum, void* stream) {
@@ -558,12 +567,24 @@ extern "C" int ldnn_bn_fwd_stats(const void* y, int M, int C, int chunks, float*
   const int rows = (M + chunks - 1) / chunks;
   const int lanes = kRowLanes;
   const size_t smem = bn_smem_bytes(C, lanes);
-  bn_stats_kernel<<<dim3(C / kSlab, chunks), kBnThreads, smem, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)y, partial, ticket, M, C, rows, gamma, beta, running_mean, running_var, nbt, save_mean,
+  bn_stats_kernel<T><<<dim3(C / kSlab, chunks), kBnThreads, smem, (cudaStream_t)stream>>>(
+      (const T*)y, partial, ticket, M, C, rows, gamma, beta, running_mean, running_var, nbt, save_mean,
       save_invstd, scale, shift, eps, momentum);
   COUNT_LAUNCH();
   LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
+}
+extern "C" int ldnn_bn_fwd_stats(const void* y, int M, int C, int chunks, float* partial, unsigned int* ticket,
+                                 const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                 long long* nbt, float* save_mean, float* save_invstd, float* scale, float* shift,
+                                 float eps, float momentum, void* stream) {
+  return bn_fwd_stats_impl<__nv_bfloat16>(y, M, C, chunks, partial, ticket, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd, scale, shift, eps, momentum, stream);
+}
+extern "C" int ldnn_bn_fwd_stats_f32(const void* y, int M, int C, int chunks, float* partial, unsigned int* ticket,
+                                 const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                 long long* nbt, float* save_mean, float* save_invstd, float* scale, float* shift,
+                                 float eps, float momentum, void* stream) {
+  return bn_fwd_stats_impl<float>(y, M, C, chunks, partial, ticket, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd, scale, shift, eps, momentum, stream);
 }
 
 extern "C" int ldnn_bn_eval_coeffs(const float* gamma, const float* beta, const float* rm, const float* rv,
@@ -574,43 +595,76 @@ extern "C" int ldnn_bn_eval_coeffs(const float* gamma, const float* beta, const 
   return LDNN_OK;
 }
 
-extern "C" int ldnn_bn_fwd_apply(const void* y, const float* scale, const float* shift, const void* residual,
+template <typename T>
+static int bn_fwd_apply_impl(const void* y, const float* scale, const float* shift, const void* residual,
                                  void* out, int M, int C, int relu, void* stream) {
   LDNN_ARG(C % 8 == 0, "bn: C %% 8");
   const long long total8 = (long long)M * C / 8;
-  bn_apply_kernel<<<grid_for(total8, 256), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)y, scale, shift, (const __nv_bfloat16*)residual, (__nv_bfloat16*)out, total8, C, relu);
+  bn_apply_kernel<T><<<grid_for(total8, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const T*)y, scale, shift, (const T*)residual, (T*)out, total8, C, relu);
   COUNT_LAUNCH();
   LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
+extern "C" int ldnn_bn_fwd_apply(const void* y, const float* scale, const float* shift, const void* residual,
+                                 void* out, int M, int C, int relu, void* stream) {
+  return bn_fwd_apply_impl<__nv_bfloat16>(y, scale, shift, residual, out, M, C, relu, stream);
+}
+extern "C" int ldnn_bn_fwd_apply_f32(const void* y, const float* scale, const float* shift, const void* residual,
+                                 void* out, int M, int C, int relu, void* stream) {
+  return bn_fwd_apply_impl<float>(y, scale, shift, residual, out, M, C, relu, stream);
+}
 
-extern "C" int ldnn_bn_bwd_reduce(const void* dout, const void* out, const void* y, const float* save_mean,
+template <typename T>
+static int bn_bwd_reduce_impl(const void* dout, const void* out, const void* y, const float* save_mean,
                                   const float* save_invstd, float* partial, unsigned int* ticket, int M, int C,
                                   int chunks, int relu, float* dgamma, float* dbeta, void* stream) {
   LDNN_ARG(C % kSlab == 0 && C <= 2048, "bn: C=%d unsupported (need C%%64==0, C<=2048)", C);
   const int rows = (M + chunks - 1) / chunks;
   const int lanes = kRowLanes;
   const size_t smem = bn_smem_bytes(C, lanes);
-  bn_bwd_reduce_kernel<<<dim3(C / kSlab, chunks), kBnThreads, smem, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, partial,
+  bn_bwd_reduce_kernel<T><<<dim3(C / kSlab, chunks), kBnThreads, smem, (cudaStream_t)stream>>>(
+      (const T*)dout, (const T*)out, (const T*)y, save_mean, save_invstd, partial,
       ticket, M, C, rows, relu, dgamma, dbeta);
   COUNT_LAUNCH();
   LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
 }
+extern "C" int ldnn_bn_bwd_reduce(const void* dout, const void* out, const void* y, const float* save_mean,
+                                  const float* save_invstd, float* partial, unsigned int* ticket, int M, int C,
+                                  int chunks, int relu, float* dgamma, float* dbeta, void* stream) {
+  return bn_bwd_reduce_impl<__nv_bfloat16>(dout, out, y, save_mean, save_invstd, partial, ticket, M, C, chunks, relu, dgamma, dbeta, stream);
+}
+extern "C" int ldnn_bn_bwd_reduce_f32(const void* dout, const void* out, const void* y, const float* save_mean,
+                                  const float* save_invstd, float* partial, unsigned int* ticket, int M, int C,
+                                  int chunks, int relu, float* dgamma, float* dbeta, void* stream) {
+  return bn_bwd_reduce_impl<float>(dout, out, y, save_mean, save_invstd, partial, ticket, M, C, chunks, relu, dgamma, dbeta, stream);
+}
 
-extern "C" int ldnn_bn_bwd_apply(const void* dout, const void* out, const void* y, const float* save_mean,
+template <typename T>
+static int bn_bwd_apply_impl(const void* dout, const void* out, const void* y, const float* save_mean,
                                  const float* save_invstd, const float* gamma, const float* dgamma,
                                  const float* dbeta, void* dy_raw, void* dres, int M, int C, int relu,
                                  int res_accumulate, void* stream) {
   const long long total8 = (long long)M * C / 8;
-  bn_bwd_apply_kernel<<<grid_for(total8, 256), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean, save_invstd, gamma,
-      dgamma, dbeta, (__nv_bfloat16*)dy_raw, (__nv_bfloat16*)dres, total8, C, relu, res_accumulate, 1.f / (float)M);
+  bn_bwd_apply_kernel<T><<<grid_for(total8, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const T*)dout, (const T*)out, (const T*)y, save_mean, save_invstd, gamma,
+      dgamma, dbeta, (T*)dy_raw, (T*)dres, total8, C, relu, res_accumulate, 1.f / (float)M);
   COUNT_LAUNCH();
   LDNN_CUDA(cudaGetLastError());
   return LDNN_OK;
+}
+extern "C" int ldnn_bn_bwd_apply(const void* dout, const void* out, const void* y, const float* save_mean,
+                                 const float* save_invstd, const float* gamma, const float* dgamma,
+                                 const float* dbeta, void* dy_raw, void* dres, int M, int C, int relu,
+                                 int res_accumulate, void* stream) {
+  return bn_bwd_apply_impl<__nv_bfloat16>(dout, out, y, save_mean, save_invstd, gamma, dgamma, dbeta, dy_raw, dres, M, C, relu, res_accumulate, stream);
+}
+extern "C" int ldnn_bn_bwd_apply_f32(const void* dout, const void* out, const void* y, const float* save_mean,
+                                 const float* save_invstd, const float* gamma, const float* dgamma,
+                                 const float* dbeta, void* dy_raw, void* dres, int M, int C, int relu,
+                                 int res_accumulate, void* stream) {
+  return bn_bwd_apply_impl<float>(dout, out, y, save_mean, save_invstd, gamma, dgamma, dbeta, dy_raw, dres, M, C, relu, res_accumulate, stream);
 }
 
 static int apply_chunks(int M, int C) {
@@ -619,80 +673,144 @@ static int apply_chunks(int M, int C) {
   return std::max(1, std::min((M + 127) / 128, std::max(1, 592 / slabs)));
 }
 
-extern "C" int ldnn_bn_fwd_apply_sums(const void* y, const float* sums, const float* gamma, const float* beta,
+template <typename T>
+static int bn_fwd_apply_sums_impl(const void* y, const float* sums, const float* gamma, const float* beta,
                                       float* running_mean, float* running_var, long long* nbt, float* save_mean,
                                       float* save_invstd, const void* residual, void* out, int M, int C, int relu,
                                       int training, float eps, float momentum, void* stream) {
   LDNN_ARG(C % kSlab == 0, "bn: C=%d unsupported (need C%%64==0)", C);
   const int chunks = apply_chunks(M, C);
   const int rows = (M + chunks - 1) / chunks;
-  LDNN_CUDA(launch_pdl(bn_apply_sums_kernel, dim3(C / kSlab, chunks), dim3(256), 0, (cudaStream_t)stream,
-                       (const __nv_bfloat16*)y, sums, gamma, beta, running_mean, running_var, nbt, save_mean,
-                       save_invstd, (const __nv_bfloat16*)residual, (__nv_bfloat16*)out, rows, C, M, relu, training, eps,
+  LDNN_CUDA(launch_pdl(bn_apply_sums_kernel<T>, dim3(C / kSlab, chunks), dim3(256), 0, (cudaStream_t)stream,
+                       (const T*)y, sums, gamma, beta, running_mean, running_var, nbt, save_mean,
+                       save_invstd, (const T*)residual, (T*)out, rows, C, M, relu, training, eps,
                        momentum));
   COUNT_LAUNCH();
   return LDNN_OK;
 }
+extern "C" int ldnn_bn_fwd_apply_sums(const void* y, const float* sums, const float* gamma, const float* beta,
+                                      float* running_mean, float* running_var, long long* nbt, float* save_mean,
+                                      float* save_invstd, const void* residual, void* out, int M, int C, int relu,
+                                      int training, float eps, float momentum, void* stream) {
+  return bn_fwd_apply_sums_impl<__nv_bfloat16>(y, sums, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd, residual, out, M, C, relu, training, eps, momentum, stream);
+}
+extern "C" int ldnn_bn_fwd_apply_sums_f32(const void* y, const float* sums, const float* gamma, const float* beta,
+                                      float* running_mean, float* running_var, long long* nbt, float* save_mean,
+                                      float* save_invstd, const void* residual, void* out, int M, int C, int relu,
+                                      int training, float eps, float momentum, void* stream) {
+  return bn_fwd_apply_sums_impl<float>(y, sums, gamma, beta, running_mean, running_var, nbt, save_mean, save_invstd, residual, out, M, C, relu, training, eps, momentum, stream);
+}
 
-extern "C" int ldnn_bn_bwd_reduce_sums(const void* dout, const void* out, const void* y, const float* save_mean,
+template <typename T>
+static int bn_bwd_reduce_sums_impl(const void* dout, const void* out, const void* y, const float* save_mean,
                                        const float* save_invstd, float* sums, int M, int C, int chunks, int relu,
                                        void* stream) {
   LDNN_ARG(C % kSlab == 0, "bn: C=%d unsupported (need C%%64==0)", C);
   const int rows = (M + chunks - 1) / chunks;
-  LDNN_CUDA(launch_pdl(bn_bwd_reduce_atomic_kernel, dim3(C / kSlab, chunks), dim3(kBnThreads), 0, (cudaStream_t)stream,
-                       (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean,
+  LDNN_CUDA(launch_pdl(bn_bwd_reduce_atomic_kernel<T>, dim3(C / kSlab, chunks), dim3(kBnThreads), 0, (cudaStream_t)stream,
+                       (const T*)dout, (const T*)out, (const T*)y, save_mean,
                        save_invstd, sums, M, C, rows, relu));
   COUNT_LAUNCH();
   return LDNN_OK;
 }
+extern "C" int ldnn_bn_bwd_reduce_sums(const void* dout, const void* out, const void* y, const float* save_mean,
+                                       const float* save_invstd, float* sums, int M, int C, int chunks, int relu,
+                                       void* stream) {
+  return bn_bwd_reduce_sums_impl<__nv_bfloat16>(dout, out, y, save_mean, save_invstd, sums, M, C, chunks, relu, stream);
+}
+extern "C" int ldnn_bn_bwd_reduce_sums_f32(const void* dout, const void* out, const void* y, const float* save_mean,
+                                       const float* save_invstd, float* sums, int M, int C, int chunks, int relu,
+                                       void* stream) {
+  return bn_bwd_reduce_sums_impl<float>(dout, out, y, save_mean, save_invstd, sums, M, C, chunks, relu, stream);
+}
 
-extern "C" int ldnn_bn_bwd_apply_sums(const void* dout, const void* out, const void* y, const float* save_mean,
+template <typename T>
+static int bn_bwd_apply_sums_impl(const void* dout, const void* out, const void* y, const float* save_mean,
                                       const float* save_invstd, const float* gamma, const float* sums, void* dy_raw,
                                       void* dres, float* dgamma, float* dbeta, int M, int C, int relu,
                                       int res_accumulate, void* stream) {
   LDNN_ARG(C % kSlab == 0, "bn: C=%d unsupported (need C%%64==0)", C);
   const int chunks = apply_chunks(M, C);
   const int rows = (M + chunks - 1) / chunks;
-  LDNN_CUDA(launch_pdl(bn_bwd_apply_sums_kernel, dim3(C / kSlab, chunks), dim3(256), 0, (cudaStream_t)stream,
-                       (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, (const __nv_bfloat16*)y, save_mean,
-                       save_invstd, gamma, sums, (__nv_bfloat16*)dy_raw, (__nv_bfloat16*)dres, dgamma, dbeta, rows, M, C,
+  LDNN_CUDA(launch_pdl(bn_bwd_apply_sums_kernel<T>, dim3(C / kSlab, chunks), dim3(256), 0, (cudaStream_t)stream,
+                       (const T*)dout, (const T*)out, (const T*)y, save_mean,
+                       save_invstd, gamma, sums, (T*)dy_raw, (T*)dres, dgamma, dbeta, rows, M, C,
                        relu, res_accumulate, 1.f / (float)M));
   COUNT_LAUNCH();
   return LDNN_OK;
 }
+extern "C" int ldnn_bn_bwd_apply_sums(const void* dout, const void* out, const void* y, const float* save_mean,
+                                      const float* save_invstd, const float* gamma, const float* sums, void* dy_raw,
+                                      void* dres, float* dgamma, float* dbeta, int M, int C, int relu,
+                                      int res_accumulate, void* stream) {
+  return bn_bwd_apply_sums_impl<__nv_bfloat16>(dout, out, y, save_mean, save_invstd, gamma, sums, dy_raw, dres, dgamma, dbeta, M, C, relu, res_accumulate, stream);
+}
+extern "C" int ldnn_bn_bwd_apply_sums_f32(const void* dout, const void* out, const void* y, const float* save_mean,
+                                      const float* save_invstd, const float* gamma, const float* sums, void* dy_raw,
+                                      void* dres, float* dgamma, float* dbeta, int M, int C, int relu,
+                                      int res_accumulate, void* stream) {
+  return bn_bwd_apply_sums_impl<float>(dout, out, y, save_mean, save_invstd, gamma, sums, dy_raw, dres, dgamma, dbeta, M, C, relu, res_accumulate, stream);
+}
 
-extern "C" int ldnn_im2col_stem(const float* x, void* col, int N, int C, int H, int W, int R, int stride, int pad,
+template <typename T>
+static int im2col_stem_impl(const float* x, void* col, int N, int C, int H, int W, int R, int stride, int pad,
                                 int Kpad, void* stream) {
   LDNN_ARG(Kpad % 64 == 0 && Kpad >= R * R * C, "im2col: Kpad=%d", Kpad);
   const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - R) / stride + 1;
   const long long total = (long long)N * P * Q * (Kpad / 8);
-  LDNN_CUDA(launch_pdl(im2col_stem_kernel, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream, x,
-                       (__nv_bfloat16*)col, N, C, H, W, R, stride, pad, P, Q, Kpad));
+  LDNN_CUDA(launch_pdl(im2col_stem_kernel<T>, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream, x,
+                       (T*)col, N, C, H, W, R, stride, pad, P, Q, Kpad));
   COUNT_LAUNCH();
   return LDNN_OK;
 }
+extern "C" int ldnn_im2col_stem(const float* x, void* col, int N, int C, int H, int W, int R, int stride, int pad,
+                                int Kpad, void* stream) {
+  return im2col_stem_impl<__nv_bfloat16>(x, col, N, C, H, W, R, stride, pad, Kpad, stream);
+}
+extern "C" int ldnn_im2col_stem_f32(const float* x, void* col, int N, int C, int H, int W, int R, int stride, int pad,
+                                int Kpad, void* stream) {
+  return im2col_stem_impl<float>(x, col, N, C, H, W, R, stride, pad, Kpad, stream);
+}
 
-extern "C" int ldnn_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
+template <typename T>
+static int maxpool_fwd_impl(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
                                 int pad, void* stream) {
   LDNN_ARG(C % 8 == 0 && k * k <= 255, "maxpool: C=%d k=%d", C, k);
   const int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
   const long long total = (long long)N * P * Q * (C / 8);
-  LDNN_CUDA(launch_pdl(maxpool_fwd_kernel, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream,
-                       (const __nv_bfloat16*)x, (__nv_bfloat16*)y, (uint8_t*)idx, N, H, W, C, k, stride, pad, P, Q));
+  LDNN_CUDA(launch_pdl(maxpool_fwd_kernel<T>, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream,
+                       (const T*)x, (T*)y, (uint8_t*)idx, N, H, W, C, k, stride, pad, P, Q));
   COUNT_LAUNCH();
   return LDNN_OK;
 }
+extern "C" int ldnn_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
+                                int pad, void* stream) {
+  return maxpool_fwd_impl<__nv_bfloat16>(x, y, idx, N, H, W, C, k, stride, pad, stream);
+}
+extern "C" int ldnn_maxpool_fwd_f32(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride,
+                                int pad, void* stream) {
+  return maxpool_fwd_impl<float>(x, y, idx, N, H, W, C, k, stride, pad, stream);
+}
 
-extern "C" int ldnn_maxpool_bwd(const void* idx, const void* dy, void* dx, int N, int H, int W, int C, int k,
+template <typename T>
+static int maxpool_bwd_impl(const void* idx, const void* dy, void* dx, int N, int H, int W, int C, int k,
                                 int stride, int pad, void* stream) {
   LDNN_ARG(idx != nullptr && C % 8 == 0, "maxpool backward needs the argmax map written by the forward pass");
   const int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
   const long long total = (long long)N * H * W * (C / 8);
-  LDNN_CUDA(launch_pdl(maxpool_bwd_kernel, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream,
-                       (const uint8_t*)idx, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, k, stride, pad, P,
+  LDNN_CUDA(launch_pdl(maxpool_bwd_kernel<T>, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream,
+                       (const uint8_t*)idx, (const T*)dy, (T*)dx, N, H, W, C, k, stride, pad, P,
                        Q));
   COUNT_LAUNCH();
   return LDNN_OK;
+}
+extern "C" int ldnn_maxpool_bwd(const void* idx, const void* dy, void* dx, int N, int H, int W, int C, int k,
+                                int stride, int pad, void* stream) {
+  return maxpool_bwd_impl<__nv_bfloat16>(idx, dy, dx, N, H, W, C, k, stride, pad, stream);
+}
+extern "C" int ldnn_maxpool_bwd_f32(const void* idx, const void* dy, void* dx, int N, int H, int W, int C, int k,
+                                int stride, int pad, void* stream) {
+  return maxpool_bwd_impl<float>(idx, dy, dx, N, H, W, C, k, stride, pad, stream);
 }
 
 // ------------------------------------------------------------------ allocation-free BN statistics
@@ -752,7 +870,7 @@ extern "C" int ldnn_bn_fwd_stats_noalloc(const void* y, int M, int C, int chunks
   const int rows = (M + chunks - 1) / chunks;
   const int lanes = kRowLanes;
   const size_t smem = bn_smem_bytes(C, lanes);
-  bn_stats_kernel<<<dim3(C / kSlab, chunks), kBnThreads, smem, st>>>((const __nv_bfloat16*)y, partial, ticket, M, C, rows, gamma, beta,
+  bn_stats_kernel<__nv_bfloat16><<<dim3(C / kSlab, chunks), kBnThreads, smem, st>>>((const __nv_bfloat16*)y, partial, ticket, M, C, rows, gamma, beta,
                                                    running_mean, running_var, nbt, save_mean, save_invstd, scale,
                                                    shift, eps, momentum);
   COUNT_LAUNCH();

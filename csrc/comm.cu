@@ -94,6 +94,15 @@ __device__ __forceinline__ void comm_barrier(const Ctx& x, unsigned int seq) {
   __syncthreads();
 }
 
+// tests only: CTA `debug_delay_block - 1` of every rank idles for `debug_delay_cycles` before its push loop, which
+// makes "a CTA reads what a DIFFERENT CTA of a peer has not pushed yet" deterministic instead of a rare race
+__device__ __forceinline__ void debug_delay(const ldnn_comm& c, const Ctx& x) {
+  if (c.debug_delay_block != 0 && c.debug_delay_block == x.block + 1) {
+    const long long t0 = clock64();
+    while ((unsigned long long)(clock64() - t0) < (unsigned long long)c.debug_delay_cycles) __nanosleep(200);
+  }
+}
+
 __device__ __forceinline__ float4 f4_scale(const float4& a, float s) { return make_float4(a.x * s, a.y * s, a.z * s, a.w * s); }
 __device__ __forceinline__ float4 f4_fma(const float4& a, float s, const float4& b) {
   return make_float4(fmaf(a.x, s, b.x), fmaf(a.y, s, b.y), fmaf(a.z, s, b.z), fmaf(a.w, s, b.w));
@@ -111,6 +120,7 @@ allreduce_fused_kernel(const ldnn_comm c, const ldnn_exchange e) {
   const bool update = (e.mode & LDNN_X_UPDATE) != 0, selfmix = (e.mode & LDNN_X_SELFMIX) != 0;
 
   comm_barrier(x, seq + 1);   // every rank's input slab is final
+  debug_delay(c, x);
 
   float4* const my_params = reinterpret_cast<float4*>(e.params[r]);
   float4* const my_m = reinterpret_cast<float4*>(e.m);
@@ -156,15 +166,21 @@ allreduce_fused_kernel(const ldnn_comm c, const ldnn_exchange e) {
     }
   }
 
-  comm_barrier(x, seq + 2);   // all pushes have landed everywhere
+  comm_barrier(x, seq + 2);   // CTA b of every rank has pushed its share: see the mapping note below
 
   // ---- local pass over the whole slab: self-mix, (per-rank) update, bf16 cast ----
+  // comm_barrier joins CTA b of this rank with CTA b of every peer ONLY, so this pass may read just what those
+  // CTAs pushed: it walks owner slice by owner slice with the push loop's own element-to-CTA mapping
+  // (i = lo_p + b*T + tid + k*stride), not the flat i = b*T + tid + k*stride (lo_p is not a multiple of stride:
+  // the flat walk would read elements pushed by some other CTA b' that may still be running).
   const bool cast = e.shadow != nullptr && (update || (e.mode & 4));
   if (selfmix || cast) {
     float4* g = reinterpret_cast<float4*>(e.grads[r]);
     const float4* rv = reinterpret_cast<const float4*>(e.recv[r]);
     __nv_bfloat16* sh = reinterpret_cast<__nv_bfloat16*>(e.shadow);
-    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n4; i += stride) {
+    for (int p = 0; p < W; ++p) {
+     const long long lo_p = min((long long)p * per, n4), hi_p = min(lo_p + per, n4);
+     for (long long i = lo_p + (long long)x.block * kCommThreads + threadIdx.x; i < hi_p; i += stride) {
       float4 val;
       if (selfmix) {
         val = f4_fma(g[i], e.self_coef, rv[i]);
@@ -180,6 +196,7 @@ allreduce_fused_kernel(const ldnn_comm c, const ldnn_exchange e) {
         val = update ? my_params[i] : g[i];
       }
       if (cast) store_bf16x4(sh + 4 * i, val);
+     }
     }
   }
 }
@@ -216,6 +233,7 @@ allreduce_nvls_kernel(const ldnn_comm c, const ldnn_exchange e, float4* const mc
   const bool update = (e.mode & LDNN_X_UPDATE) != 0;
 
   comm_barrier(x, seq + 1);   // every rank's input slab is final
+  debug_delay(c, x);
 
   float4* const my_params = reinterpret_cast<float4*>(e.params[r]);
   float4* const my_m = reinterpret_cast<float4*>(e.m);
@@ -253,7 +271,11 @@ allreduce_nvls_kernel(const ldnn_comm c, const ldnn_exchange e, float4* const mc
   if (cast) {
     const float4* src = update ? my_params : reinterpret_cast<const float4*>(e.grads[r]);
     __nv_bfloat16* sh = reinterpret_cast<__nv_bfloat16*>(e.shadow);
-    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n4; i += stride) store_bf16x4(sh + 4 * i, src[i]);
+    for (int p = 0; p < W; ++p) {       // owner slice by owner slice, same element-to-CTA mapping as the pushes
+      const long long lo_p = min((long long)p * per, n4), hi_p = min(lo_p + per, n4);
+      for (long long i = lo_p + (long long)x.block * kCommThreads + threadIdx.x; i < hi_p; i += stride)
+        store_bf16x4(sh + 4 * i, src[i]);
+    }
   }
 }
 

@@ -76,4 +76,38 @@ __device__ __forceinline__ uint4 float_to_bf16x8(const float (&f)[8]) {
   return u;
 }
 
+// ---- element-type generic accessors: 8 consecutive channels of an activation tensor -> fp32 registers.
+// bf16 storage = one 16-byte access; fp32 storage (the TF32 path) = two.
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
+  bf16x8_to_float(*reinterpret_cast<const uint4*>(p), f);
+}
+__device__ __forceinline__ void load8(const float* p, float (&f)[8]) {
+  const float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
+  *reinterpret_cast<uint4*>(p) = float_to_bf16x8(f);
+}
+__device__ __forceinline__ void store8(float* p, const float (&f)[8]) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(f[0], f[1], f[2], f[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(f[4], f[5], f[6], f[7]);
+}
+__device__ __forceinline__ void load2(const __nv_bfloat16* p, float& a, float& b) {
+  const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+  a = t.x; b = t.y;
+}
+__device__ __forceinline__ void load2(const float* p, float& a, float& b) {
+  const float2 t = *reinterpret_cast<const float2*>(p);
+  a = t.x; b = t.y;
+}
+__device__ __forceinline__ void store2(__nv_bfloat16* p, float a, float b) {
+  *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b);
+}
+__device__ __forceinline__ void store2(float* p, float a, float b) { *reinterpret_cast<float2*>(p) = make_float2(a, b); }
+__device__ __forceinline__ void store1(__nv_bfloat16* p, float a) { *p = __float2bfloat16(a); }
+__device__ __forceinline__ void store1(float* p, float a) { *p = a; }
+// value as it will be read back from storage (bf16 rounds, fp32 is exact)
+__device__ __forceinline__ float stored_value(const __nv_bfloat16*, float a) { return __bfloat162float(__float2bfloat16(a)); }
+__device__ __forceinline__ float stored_value(const float*, float a) { return a; }
+
 }  // namespace ldnn

@@ -46,20 +46,32 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
-// bf16 tensor, up to 4 dims, innermost contiguous, 128B swizzle, zero OOB fill.
+// TMA element type of the fp32 (TF32) path.  FLOAT32 hands the raw fp32 bits to the tensor core, which reads
+// the upper 19 (truncation); TFLOAT32 makes the TMA unit convert to TF32 while it copies.  LDNN_TF32_TMA=
+// float32|tfloat32 picks one (default tfloat32).
+static CUtensorMapDataType tf32_map_type() {
+  static int kind = -1;
+  if (kind < 0) { const char* e = getenv("LDNN_TF32_TMA"); kind = (e && (e[0] == 'f' || e[0] == 'F')) ? 0 : 1; }
+  return kind ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+}
+
+// bf16 (esize 2) or fp32 (esize 4) tensor, up to 4 dims, innermost contiguous, 128B swizzle, zero OOB fill.
+// mn32 = the operand is read MN-major by a kind::tf32 MMA: 128-byte swizzle with 32-byte atoms (see ptx.cuh).
 static int make_map(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_elems,
-                    const uint32_t* box) {
+                    const uint32_t* box, int esize, bool mn32 = false) {
   EncodeTiledFn enc = get_encode();
   LDNN_ARG(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
   cuuint64_t gdim[4], gstr[3];
   cuuint32_t bx[4], es[4];
   for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
-  for (int i = 1; i < rank; ++i) gstr[i - 1] = strides_elems[i] * 2;
+  for (int i = 1; i < rank; ++i) gstr[i - 1] = strides_elems[i] * (uint64_t)esize;
   LDNN_ARG((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16-byte aligned", base);
   for (int i = 0; i < rank - 1; ++i) LDNN_ARG(gstr[i] % 16 == 0, "TMA stride %d = %llu B not a multiple of 16", i,
                                               (unsigned long long)gstr[i]);
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstr, bx, es,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = enc(m, esize == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : tf32_map_type(), rank, const_cast<void*>(base), gdim, gstr, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   (mn32 && esize == 4) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   LDNN_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rank %d dims %llu %llu box %u %u)", (int)r, rank,
            (unsigned long long)gdim[0], (unsigned long long)gdim[1], bx[0], bx[1]);
@@ -82,6 +94,7 @@ struct Launch {
 };
 struct Plan {
   int mode, block_n, cluster = 1, lite = 0;
+  int tf32 = 0;                             // fp32 storage + kind::tf32 (desc.dtype == 1)
   int pair = 0;                             // cluster == 2 run as a cta_group::2 pair (desc.cluster == -2; staged)
   std::vector<Launch> launches;
   void* out;
@@ -117,6 +130,9 @@ static int pick_splits(int tiles, int iters, int requested) {
 // Builds every launch of a plan.  `dry` = only sizes (no tensor maps, pointers may be null).
 static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   LDNN_ARG(d.mode >= 0 && d.mode <= 2, "bad conv mode %d", d.mode);
+  LDNN_ARG(d.dtype == 0 || d.dtype == 1, "bad conv dtype %d (0 = bf16, 1 = fp32 storage / TF32 MMA)", d.dtype);
+  const int esize = d.dtype == 1 ? 4 : 2;   // bytes per activation / weight element
+  const int KE = 128 / esize;               // elements per 128-byte swizzle row = K block of a pipeline stage
   LDNN_ARG(d.Cin % 64 == 0 && d.Cout % 64 == 0, "Cin=%d / Cout=%d must be multiples of 64", d.Cin, d.Cout);
   LDNN_ARG(d.stride == 1 || d.stride == 2, "stride %d unsupported", d.stride);
   LDNN_ARG(d.R * d.R <= 12, "filter %dx%d too large for the tap table", d.R, d.R);
@@ -138,7 +154,7 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   }
   LDNN_ARG(bn_ == 64 || bn_ == 128 || bn_ == 256, "block_n %d", bn_);
   LDNN_ARG(n_total % bn_ == 0, "N=%d not a multiple of block_n=%d", n_total, bn_);
-  plan.mode = d.mode; plan.block_n = bn_;
+  plan.mode = d.mode; plan.block_n = bn_; plan.tf32 = d.dtype == 1;
   plan.lite = d.lite ? 1 : 0;
   plan.cluster = ((d.cluster == 2 || d.cluster == -2) && d.mode != MODE_WGRAD && bn_ >= 128) ? 2 : 1;
   plan.pair = (d.cluster == -2 && plan.cluster == 2) ? 1 : 0;
@@ -150,32 +166,34 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   memset(&plan.fuse, 0, sizeof(plan.fuse));
   if (d.mode == MODE_DGRAD && d.fuse_sums) {
     LDNN_ARG(d.fuse_out && d.fuse_y && d.fuse_mean && d.fuse_invstd, "dgrad BN-backward fusion needs out/y/mean/invstd");
-    plan.fuse.out = reinterpret_cast<const __nv_bfloat16*>(d.fuse_out);
-    plan.fuse.y = reinterpret_cast<const __nv_bfloat16*>(d.fuse_y);
+    plan.fuse.out = d.fuse_out;
+    plan.fuse.y = d.fuse_y;
     plan.fuse.mean = d.fuse_mean; plan.fuse.invstd = d.fuse_invstd; plan.fuse.sums = d.fuse_sums;
     plan.fuse.relu = d.fuse_relu;
   }
 
-  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(d.x);
-  const __nv_bfloat16* yb = reinterpret_cast<const __nv_bfloat16*>(d.y);
+  const char* xb = reinterpret_cast<const char*>(d.x);
+  const char* yb = reinterpret_cast<const char*>(d.y);
 
   // parity views of x for strided convs: view (hp,wp) has rows h = 2a+hp
+  const bool mn_act = d.mode == MODE_WGRAD;            // operands read MN-major: wgrad x and dy, dgrad weights
+  const bool mn_w = d.mode == MODE_DGRAD;
   auto x_view_map = [&](CUtensorMap* m, int hp, int wp, const uint32_t* box) -> int {
     const int s = d.stride;
     uint64_t dims[4] = {(uint64_t)d.Cin, (uint64_t)cdiv(d.W - wp, s), (uint64_t)cdiv(d.H - hp, s), (uint64_t)d.N};
     uint64_t str[4] = {1, (uint64_t)s * d.Cin, (uint64_t)s * d.W * d.Cin, (uint64_t)d.H * d.W * d.Cin};
-    return make_map(m, xb + ((size_t)hp * d.W + wp) * d.Cin, 4, dims, str, box);
+    return make_map(m, xb + ((size_t)hp * d.W + wp) * d.Cin * esize, 4, dims, str, box, esize, mn_act);
   };
   auto y_map = [&](CUtensorMap* m, const uint32_t* box) -> int {
     uint64_t dims[4] = {(uint64_t)d.Cout, (uint64_t)Q, (uint64_t)P, (uint64_t)d.N};
     uint64_t str[4] = {1, (uint64_t)d.Cout, (uint64_t)Q * d.Cout, (uint64_t)P * Q * d.Cout};
-    return make_map(m, yb, 4, dims, str, box);
+    return make_map(m, yb, 4, dims, str, box, esize, mn_act);
   };
   auto w_map = [&](CUtensorMap* m, uint32_t box_rows) -> int {
     uint64_t dims[2] = {(uint64_t)T * d.Cin, (uint64_t)d.Cout};
     uint64_t str[2] = {1, (uint64_t)T * d.Cin};
-    uint32_t box[2] = {64, box_rows};
-    return make_map(m, d.w, 2, dims, str, box);
+    uint32_t box[2] = {(uint32_t)KE, box_rows};
+    return make_map(m, d.w, 2, dims, str, box, esize, mn_w);
   };
   // forward-style tap table: input row = stride*p - pad + r
   auto fwd_taps = [&](ConvClass& c) {
@@ -197,19 +215,21 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   p.accumulate = d.accumulate;
   p.n_total = n_total;
   p.num_classes = 1;
-  // K-major SW128 tile: 8-row groups 1024 B apart; MN-major: 64-wide MN blocks 8192 B apart,
-  // 8-row K groups 1024 B apart.
-  p.a_lbo = d.a_lbo ? d.a_lbo : (d.mode == MODE_WGRAD ? 8192u : 16u);
-  p.a_sbo = d.a_sbo ? d.a_sbo : 1024u;
-  p.b_lbo = d.b_lbo ? d.b_lbo : (d.mode == MODE_FPROP ? 16u : 8192u);
-  p.b_sbo = d.b_sbo ? d.b_sbo : 1024u;
+  // K-major SW128 tile: 8-row groups 1024 B apart; MN-major: KE-wide MN blocks (128 B x KE K-rows = 8192 B
+  // bf16 / 4096 B fp32) apart, 8-row K groups 1024 B apart.
+  const uint32_t mn_box = 128u * (uint32_t)KE;
+  p.a_lbo = d.a_lbo ? d.a_lbo : (d.mode == MODE_WGRAD ? mn_box : 16u);
+  const uint32_t mn_sbo = esize == 4 ? 512u : 1024u;   // K-row groups of an MN-major box: 8 rows (bf16) / 4 rows (fp32)
+  p.a_sbo = d.a_sbo ? d.a_sbo : (d.mode == MODE_WGRAD ? mn_sbo : 1024u);
+  p.b_lbo = d.b_lbo ? d.b_lbo : (d.mode == MODE_FPROP ? 16u : mn_box);
+  p.b_sbo = d.b_sbo ? d.b_sbo : (d.mode == MODE_FPROP ? 1024u : mn_sbo);
   size_t scratch_floats = 0, tickets = 0;
 
   if (d.mode == MODE_FPROP) {
     ConvClass& c = p.cls[0];
     pixel_box(Q, P, d.N, 128, p, c);
     fwd_taps(c);
-    p.kb_per_tap = d.Cin / 64; p.red_ch = d.Cin;
+    p.kb_per_tap = d.Cin / KE; p.red_ch = d.Cin;
     c.iters_total = T * p.kb_per_tap;
     c.out_base = 0; p.sW = d.Cout; p.sH = (long long)Q * d.Cout; p.sN = (long long)P * Q * d.Cout;
     const int m_tiles = c.tiles_w * c.tiles_h * cdiv(d.N, p.bn), n_tiles = d.Cout / bn_;
@@ -219,7 +239,7 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
     if (c.splits > 1) { scratch_floats = (size_t)m_tiles * n_tiles * c.splits * 128 * bn_; tickets = (size_t)m_tiles * n_tiles; }
     L.grid = dim3(m_tiles, n_tiles, c.splits);
     if (!dry) {
-      uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+      uint32_t box[4] = {(uint32_t)KE, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
       const int nviews = d.stride == 1 ? 1 : 4;
       for (int v = 0; v < 4; ++v) {
         int rc = x_view_map(&L.maps.act[v], v < nviews ? v / 2 : 0, v < nviews ? v % 2 : 0, box);
@@ -231,7 +251,7 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
     if (plan.cluster == 2) LDNN_ARG(m_tiles % 2 == 0, "cluster=2 needs an even number of M tiles (%d)", m_tiles);
   } else if (d.mode == MODE_DGRAD) {
     // one class per output parity (1 class for stride 1), all in one launch
-    p.kb_per_tap = d.Cout / 64; p.red_ch = d.Cout;
+    p.kb_per_tap = d.Cout / KE; p.red_ch = d.Cout;
     p.sW = (long long)d.stride * d.Cin; p.sH = (long long)d.stride * d.W * d.Cin; p.sN = (long long)d.H * d.W * d.Cin;
     const int n_tiles = d.Cin / bn_;
     int ncls = 0, m_total = 0, covered = 0;
@@ -283,15 +303,15 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
     if (p.max_splits > 1) { scratch_floats = (size_t)m_total * n_tiles * p.max_splits * 128 * bn_; tickets = (size_t)m_total * n_tiles; }
     L.grid = dim3(m_total, n_tiles, p.max_splits);
     if (!dry) {
-      uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+      uint32_t box[4] = {(uint32_t)KE, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
       for (int v = 0; v < 4; ++v) { int rc = y_map(&L.maps.act[v], box); if (rc) return rc; }
-      int rc = w_map(&L.maps.other, 64);
+      int rc = w_map(&L.maps.other, KE);
       if (rc) return rc;
     }
   } else {
     LDNN_ARG(d.Cout % 128 == 0 || d.Cout == 64, "wgrad needs Cout %% 128 == 0 (or 64)");
     ConvClass& c = p.cls[0];
-    pixel_box(Q, P, d.N, 64, p, c);
+    pixel_box(Q, P, d.N, KE, p, c);
     fwd_taps(c);
     c.iters_total = c.tiles_w * c.tiles_h * cdiv(d.N, p.bn);
     p.sN = (long long)T * d.Cin;     // row stride of dw
@@ -307,7 +327,7 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
     }
     L.grid = dim3(m_tiles, n_tiles, T * c.splits);
     if (!dry) {
-      uint32_t box[4] = {64, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+      uint32_t box[4] = {(uint32_t)KE, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
       const int nviews = d.stride == 1 ? 1 : 4;
       for (int v = 0; v < 4; ++v) {
         int rc = x_view_map(&L.maps.act[v], v < nviews ? v / 2 : 0, v < nviews ? v % 2 : 0, box);
@@ -323,13 +343,13 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   return LDNN_OK;
 }
 
-template <int MODE, int BN, int CL, bool LITE>
+template <typename ET, int MODE, int BN, int CL, bool LITE>
 static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
   using Cfg = ConvCfg<BN>;
   constexpr int kSmem = LITE ? Cfg::kLiteSmemBytes : Cfg::kSmemBytes;
   static bool configured = false;
   if (!configured) {
-    LDNN_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<MODE, BN, CL, LITE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    LDNN_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<ET, MODE, BN, CL, LITE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    kSmem));
     configured = true;
   }
@@ -350,35 +370,42 @@ static int launch_one(const Launch& L, const Plan& pl, cudaStream_t st) {
     ++na;
   }
   cfg.attrs = attr; cfg.numAttrs = na;
-  LDNN_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<MODE, BN, CL, LITE>, L.maps, L.p, pl.out, pl.addend,
+  LDNN_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<ET, MODE, BN, CL, LITE>, L.maps, L.p, pl.out, pl.addend,
                                pl.scratch ? pl.scratch + L.scratch_off : nullptr,
                                pl.tickets ? pl.tickets + L.ticket_off : nullptr, pl.stats, pl.fuse));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return LDNN_OK;
 }
 
-template <int MODE, int BN>
+template <typename ET, int MODE, int BN>
 static int launch_variant(const Launch& L, const Plan& pl, cudaStream_t st) {
-  if (pl.lite) return launch_one<MODE, BN, 1, true>(L, pl, st);
-  return launch_one<MODE, BN, 1, false>(L, pl, st);
+  if (pl.lite) return launch_one<ET, MODE, BN, 1, true>(L, pl, st);
+  return launch_one<ET, MODE, BN, 1, false>(L, pl, st);
 }
 
-template <int MODE>
+template <typename ET, int MODE>
 static int launch_bn(const Launch& L, const Plan& pl, cudaStream_t st) {
   if (pl.cluster == 2 && MODE != MODE_WGRAD) {      // cluster path: 128/256-wide tiles, full pipeline
     constexpr int M2 = MODE == MODE_WGRAD ? MODE_FPROP : MODE;
     if (pl.pair) {                                   // cta_group::2 pair (UMMA_M = 256), staged
-      if (pl.block_n == 128) return launch_one<M2, 128, -2, false>(L, pl, st);
-      return launch_one<M2, 256, -2, false>(L, pl, st);
+      if (pl.block_n == 128) return launch_one<ET, M2, 128, -2, false>(L, pl, st);
+      return launch_one<ET, M2, 256, -2, false>(L, pl, st);
     }
-    if (pl.block_n == 128) return launch_one<M2, 128, 2, false>(L, pl, st);
-    return launch_one<M2, 256, 2, false>(L, pl, st);
+    if (pl.block_n == 128) return launch_one<ET, M2, 128, 2, false>(L, pl, st);
+    return launch_one<ET, M2, 256, 2, false>(L, pl, st);
   }
   switch (pl.block_n) {
-    case 64: return launch_variant<MODE, 64>(L, pl, st);
-    case 128: return launch_variant<MODE, 128>(L, pl, st);
-    default: return launch_variant<MODE, 256>(L, pl, st);
+    case 64: return launch_variant<ET, MODE, 64>(L, pl, st);
+    case 128: return launch_variant<ET, MODE, 128>(L, pl, st);
+    default: return launch_variant<ET, MODE, 256>(L, pl, st);
   }
+}
+
+template <typename ET>
+static int launch_mode(const Launch& L, const Plan& pl, cudaStream_t st) {
+  if (pl.mode == MODE_FPROP) return launch_bn<ET, MODE_FPROP>(L, pl, st);
+  if (pl.mode == MODE_DGRAD) return launch_bn<ET, MODE_DGRAD>(L, pl, st);
+  return launch_bn<ET, MODE_WGRAD>(L, pl, st);
 }
 
 }  // namespace ldnn
@@ -428,10 +455,7 @@ extern "C" int ldnn_conv_plan_run(void* plan, void* stream) {
   Plan* pl = reinterpret_cast<Plan*>(plan);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   for (const Launch& L : pl->launches) {
-    int rc;
-    if (pl->mode == MODE_FPROP) rc = launch_bn<MODE_FPROP>(L, *pl, st);
-    else if (pl->mode == MODE_DGRAD) rc = launch_bn<MODE_DGRAD>(L, *pl, st);
-    else rc = launch_bn<MODE_WGRAD>(L, *pl, st);
+    const int rc = pl->tf32 ? launch_mode<float>(L, *pl, st) : launch_mode<__nv_bfloat16>(L, *pl, st);
     if (rc) return rc;
   }
   return LDNN_OK;

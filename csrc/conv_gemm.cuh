@@ -7,9 +7,15 @@
 //   DGRAD  dx[pix, ci]  = sum_{tap, co} dy[pix (-) tap, co] * w[co, tap, ci]      (B read MN-major: no transposed copy)
 //   WGRAD  dw[co,tap,ci]= sum_{pix}     dy[pix, co] * x[pix (+) tap, ci]           (A and B read MN-major)
 //
-// Activations are NHWC bf16, weights KRSC bf16 ("[Cout][R][S][Cin]").  There is no im2col
+// Two element types, one kernel template (ET):
+//   bf16  — activations NHWC bf16, weights KRSC bf16, tcgen05.mma kind::f16  (UMMA_K = 16)
+//   float — activations NHWC fp32, weights KRSC fp32 read straight from the master slab, kind::tf32 (UMMA_K = 8):
+//           the reference's own precision (fp32 storage, TF32 convolutions — torch's default cudnn.allow_tf32).
+// A 128-byte swizzle row holds KE = 64 bf16 / 32 fp32 elements, so a pipeline stage carries one KE-wide K block:
+// same bytes, same 4 MMAs per stage, same shared-memory descriptors in both precisions.
+// Activations are NHWC, weights KRSC ("[Cout][R][S][Cin]").  There is no im2col
 // buffer: for every filter tap the A tile is a *shifted 4-D TMA box* of the activation tensor
-// (channels x w x h x n = 64 x bw x bh x bn, bw*bh*bn pixels), and the TMA unit's out-of-bounds
+// (channels x w x h x n = KE x bw x bh x bn, bw*bh*bn pixels), and the TMA unit's out-of-bounds
 // zero fill provides the padding.  Stride-2 convolutions use four parity views of the input
 // (one tensor map per (h%2, w%2)), which turns them into the same shifted-box loads.
 // Accumulators live in TMEM (128 lanes x BLOCK_N fp32 columns); a single elected thread issues
@@ -48,9 +54,9 @@ struct ConvClass {
 };
 
 struct ConvParams {
-  int bw, bh, bn;          // pixel box (w, h, n); bw*bh*bn = 128 (fprop/dgrad M tile) or 64 (wgrad K block)
+  int bw, bh, bn;          // pixel box (w, h, n); bw*bh*bn = 128 (fprop/dgrad M tile) or KE (wgrad K block)
   int Nd;                  // batch (store mask)
-  int kb_per_tap;          // fprop/dgrad: reduction channels / 64
+  int kb_per_tap;          // fprop/dgrad: reduction channels / KE
   int red_ch;              // fprop: Cin, dgrad: Cout (weight column stride per tap); wgrad: Cout (row mask)
   int n_total;             // total N of the GEMM (fprop: Cout, dgrad: Cin, wgrad: Cin)
   int num_classes;
@@ -66,8 +72,8 @@ struct ConvParams {
 // sums += (sum dy, sum dy * xhat)) is folded into this epilogue when this dgrad is the last
 // contribution to dx — one launch fewer per layer and dx is not re-read.
 struct BnBwdFuse {
-  const __nv_bfloat16* out;    // post-activation output of the owning layer (ReLU mask), same shape as dx
-  const __nv_bfloat16* y;      // its pre-BN conv output
+  const void* out;             // post-activation output of the owning layer (ReLU mask), same shape/type as dx
+  const void* y;               // its pre-BN conv output
   const float* mean;
   const float* invstd;
   float* sums;                 // [2][C]
@@ -77,6 +83,19 @@ struct BnBwdFuse {
 struct ConvMaps {
   CUtensorMap act[4];   // shifted operand (x for fprop/wgrad, dy for dgrad), one per parity view
   CUtensorMap other;    // weights (fprop/dgrad, 2-D) or dy (wgrad, 4-D)
+};
+
+// element-type traits of the MMA operands
+template <typename ET> struct ElemTraits;
+template <> struct ElemTraits<__nv_bfloat16> {
+  static constexpr int kKE = 64;            // elements per 128-byte swizzle row = K block of a stage
+  static constexpr int kUmmaK = 16;
+  static constexpr bool kTf32 = false;
+};
+template <> struct ElemTraits<float> {
+  static constexpr int kKE = 32;
+  static constexpr int kUmmaK = 8;
+  static constexpr bool kTf32 = true;
 };
 
 template <int BLOCK_N>
@@ -103,12 +122,15 @@ struct ConvCfg {
 // CL = -2 ("pair", staged — see NEXT.md 1a): the two CTAs of a TPC run ONE tcgen05.mma.cta_group::2 of UMMA_M = 256:
 // each CTA loads its own A box and only ITS HALF of the B tile (no multicast: half the B bytes enter each SM), the
 // leader CTA issues the MMAs for both, each CTA's TMEM receives its own 128 rows and its epilogue is unchanged.
-template <int MODE, int BLOCK_N, int CL, bool LITE>
+template <typename ET, int MODE, int BLOCK_N, int CL, bool LITE>
 __global__ void __launch_bounds__(LITE ? 192 : 320, LITE ? 2 : 1)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void* __restrict__ out,
                  const void* __restrict__ addend, float* __restrict__ scratch, unsigned int* __restrict__ tickets,
                  float* __restrict__ stats, const BnBwdFuse fuse) {
   using Cfg = ConvCfg<BLOCK_N>;
+  using ETr = ElemTraits<ET>;
+  constexpr int KE = ETr::kKE;                  // K block of a stage (and width of an MN-major box), in elements
+  constexpr int kMnBox = 128 * KE;              // bytes of one MN-major box: KE (MN) x KE (K) elements = 128 B x KE rows
   constexpr bool PAIR = CL < 0;                 // cta_group::2 pair
   constexpr int CLN = CL < 0 ? -CL : CL;        // CTAs per cluster
   static_assert(!PAIR || (CLN == 2 && MODE != MODE_WGRAD && BLOCK_N >= 128 && !LITE), "pair: fprop/dgrad, N >= 128");
@@ -193,61 +215,69 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
         if (PAIR) {
           const int tap = it / p.kb_per_tap, kb = it - tap * p.kb_per_tap;
           const TapEntry te = kc.taps[tap];
-          tma_load_4d_2sm(sA, &maps.act[te.map], &full_bar[stage], kb * 64, w0 + te.dw, h0 + te.dh, nn0);
+          tma_load_4d_2sm(sA, &maps.act[te.map], &full_bar[stage], kb * KE, w0 + te.dw, h0 + te.dh, nn0);
           if (MODE == MODE_FPROP) {
             // my BLOCK_N/2 weight rows, at the SAME smem offset in both CTAs (the MMA reads half of B from each)
-            tma_load_2d_2sm(sB, &maps.other, &full_bar[stage], te.wtap * p.red_ch + kb * 64,
+            tma_load_2d_2sm(sB, &maps.other, &full_bar[stage], te.wtap * p.red_ch + kb * KE,
                             n0 + (int)crank * (BLOCK_N / 2));
           } else {
 #pragma unroll
-            for (int jj = 0; jj < BLOCK_N / 128; ++jj) {       // my half of the 64-wide ci boxes
-              const int j = (int)crank * (BLOCK_N / 128) + jj;
-              tma_load_2d_2sm(sB + jj * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64, kb * 64);
+            for (int jj = 0; jj < BLOCK_N / (2 * KE); ++jj) {       // my half of the KE-wide ci boxes
+              const int j = (int)crank * (BLOCK_N / (2 * KE)) + jj;
+              tma_load_2d_2sm(sB + jj * kMnBox, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * KE, kb * KE);
             }
           }
         } else if (MODE == MODE_FPROP || MODE == MODE_DGRAD) {
           const int tap = it / p.kb_per_tap, kb = it - tap * p.kb_per_tap;
           const TapEntry te = kc.taps[tap];
-          tma_load_4d(sA, &maps.act[te.map], &full_bar[stage], kb * 64, w0 + te.dw, h0 + te.dh, nn0);
+          tma_load_4d(sA, &maps.act[te.map], &full_bar[stage], kb * KE, w0 + te.dw, h0 + te.dh, nn0);
           if (MODE == MODE_FPROP) {
-            // weights [Cout rows][taps*Cin cols], K-major: one box of 64 cols x BLOCK_N rows
+            // weights [Cout rows][taps*Cin cols], K-major: one box of KE cols x BLOCK_N rows
             if (CLN == 1) {
-              tma_load_2d(sB, &maps.other, &full_bar[stage], te.wtap * p.red_ch + kb * 64, n0);
+              tma_load_2d(sB, &maps.other, &full_bar[stage], te.wtap * p.red_ch + kb * KE, n0);
             } else {          // my half of the rows, delivered to both CTAs
               constexpr int kHalfRows = BLOCK_N / CLN;
               tma_load_2d_mc(sB + crank * kHalfRows * 128, &maps.other, &full_bar[stage],
-                             te.wtap * p.red_ch + kb * 64, n0 + (int)crank * kHalfRows, kMcMask);
+                             te.wtap * p.red_ch + kb * KE, n0 + (int)crank * kHalfRows, kMcMask);
             }
           } else {
-            // weights [Cout rows][taps*Cin cols]; B[n=ci, k=co] is MN-major: boxes of 64 ci x 64 co
+            // weights [Cout rows][taps*Cin cols]; B[n=ci, k=co] is MN-major: boxes of KE ci x KE co
 #pragma unroll
-            for (int j = 0; j < BLOCK_N / 64; ++j) {
+            for (int j = 0; j < BLOCK_N / KE; ++j) {
               if (CLN == 1)
-                tma_load_2d(sB + j * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64, kb * 64);
+                tma_load_2d(sB + j * kMnBox, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * KE, kb * KE);
               else if ((j % CLN) == (int)crank)      // boxes dealt round-robin to the cluster's CTAs
-                tma_load_2d_mc(sB + j * 8192, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * 64,
-                               kb * 64, kMcMask);
+                tma_load_2d_mc(sB + j * kMnBox, &maps.other, &full_bar[stage], te.wtap * p.n_total + n0 + j * KE,
+                               kb * KE, kMcMask);
             }
           }
         } else {
           decode(it, w0, h0, nn0);
           const TapEntry te = kc.taps[tap_fixed];
-          // A = dy[pix][co]  (MN-major, two 64-channel boxes) ; B = x[pix (+) tap][ci] (MN-major)
-          tma_load_4d(sA, &maps.other, &full_bar[stage], m_tile * 128, w0, h0, nn0);
-          tma_load_4d(sA + 8192, &maps.other, &full_bar[stage], m_tile * 128 + 64, w0, h0, nn0);
+          // A = dy[pix][co]  (MN-major, 128/KE boxes of KE channels) ; B = x[pix (+) tap][ci] (MN-major)
 #pragma unroll
-          for (int j = 0; j < BLOCK_N / 64; ++j)
-            tma_load_4d(sB + j * 8192, &maps.act[te.map], &full_bar[stage], n0 + j * 64, w0 + te.dw, h0 + te.dh, nn0);
+          for (int j = 0; j < 128 / KE; ++j)
+            tma_load_4d(sA + j * kMnBox, &maps.other, &full_bar[stage], m_tile * 128 + j * KE, w0, h0, nn0);
+#pragma unroll
+          for (int j = 0; j < BLOCK_N / KE; ++j)
+            tma_load_4d(sB + j * kMnBox, &maps.act[te.map], &full_bar[stage], n0 + j * KE, w0 + te.dw, h0 + te.dh, nn0);
         }
         if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc_bf16(PAIR ? 256 : 128, BLOCK_N, MODE == MODE_WGRAD ? 1u : 0u,
-                                               MODE == MODE_FPROP ? 0u : 1u);
-    constexpr uint32_t a_kstep = (MODE == MODE_WGRAD) ? 2048u : 32u;
-    constexpr uint32_t b_kstep = (MODE == MODE_FPROP) ? 32u : 2048u;
+    constexpr uint32_t idesc = make_idesc(ETr::kTf32 ? 2u : 1u, PAIR ? 256 : 128, BLOCK_N, MODE == MODE_WGRAD ? 1u : 0u,
+                                          MODE == MODE_FPROP ? 0u : 1u);
+    // one MMA consumes UMMA_K of K: 32 bytes along a K-major row, UMMA_K 128-byte rows of an MN-major box
+    constexpr uint32_t kMnStep = ETr::kUmmaK * 128u;
+    constexpr uint32_t a_kstep = (MODE == MODE_WGRAD) ? kMnStep : 32u;
+    constexpr uint32_t b_kstep = (MODE == MODE_FPROP) ? 32u : kMnStep;
+    // MN-major fp32 operands must sit in the 32-byte-atom flavour of the 128-byte swizzle (4-row atoms, SBO 512);
+    // the host builds their tensor maps with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B to match
+    constexpr uint32_t kMnLayout = ETr::kTf32 ? kLayoutSw128Base32 : kLayoutSw128;
+    constexpr uint32_t a_layout = (MODE == MODE_WGRAD) ? kMnLayout : kLayoutSw128;
+    constexpr uint32_t b_layout = (MODE == MODE_FPROP) ? kLayoutSw128 : kMnLayout;
     int stage = 0; uint32_t phase = 0;
     for (int it = it_begin; it < it_end && !(PAIR && crank != 0); ++it) {      // pair: only the leader issues
       mbar_wait(&full_bar[stage], phase);
@@ -257,10 +287,16 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
         const uint32_t sB = sA + Cfg::kABytes;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          const uint64_t da = make_smem_desc_sw128(sA + k * a_kstep, p.a_lbo, p.a_sbo);
-          const uint64_t db = make_smem_desc_sw128(sB + k * b_kstep, p.b_lbo, p.b_sbo);
-          if (PAIR) umma_bf16_2sm(tmem_base, da, db, idesc, (it > it_begin || k > 0) ? 1u : 0u);
-          else umma_bf16(tmem_base, da, db, idesc, (it > it_begin || k > 0) ? 1u : 0u);
+          const uint64_t da = make_smem_desc(sA + k * a_kstep, p.a_lbo, p.a_sbo, a_layout);
+          const uint64_t db = make_smem_desc(sB + k * b_kstep, p.b_lbo, p.b_sbo, b_layout);
+          const uint32_t acc = (it > it_begin || k > 0) ? 1u : 0u;
+          if (ETr::kTf32) {
+            if (PAIR) umma_tf32_2sm(tmem_base, da, db, idesc, acc);
+            else umma_tf32(tmem_base, da, db, idesc, acc);
+          } else {
+            if (PAIR) umma_bf16_2sm(tmem_base, da, db, idesc, acc);
+            else umma_bf16(tmem_base, da, db, idesc, acc);
+          }
         }
         if (PAIR) {
           umma_commit_2sm_mc(&empty_bar[stage], kMcMask);                   // frees the stage in BOTH CTAs
@@ -316,33 +352,23 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
           for (int i = 0; i < 8; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
         }
       } else {
-        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + row_off + n0 + col0;
-        const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(addend) + row_off + n0 + col0;
+        ET* o = reinterpret_cast<ET*>(out) + row_off + n0 + col0;
+        const ET* a = reinterpret_cast<const ET*>(addend) + row_off + n0 + col0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           float f[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) f[j] = v[8 * i + j];
           if (p.accumulate) {
-            uint4 av = *reinterpret_cast<const uint4*>(a + 8 * i);
-            const __nv_bfloat162* ab = reinterpret_cast<const __nv_bfloat162*>(&av);
+            float t[8];
+            load8(a + 8 * i, t);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              float2 t = __bfloat1622float2(ab[j]);
-              f[2 * j] += t.x; f[2 * j + 1] += t.y;
-            }
+            for (int j = 0; j < 8; ++j) f[j] += t[j];
           }
-          uint4 ov;
-          __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(&ov);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) ob[j] = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
-          *reinterpret_cast<uint4*>(o + 8 * i) = ov;
+          store8(o + 8 * i, f);
           if (MODE == MODE_DGRAD) {            // hand the stored (rounded) values back for the fused BN reduce
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float2 t = __bfloat1622float2(ob[j]);
-              v[8 * i + 2 * j] = t.x; v[8 * i + 2 * j + 1] = t.y;
-            }
+            for (int j = 0; j < 8; ++j) v[8 * i + j] = stored_value(o, f[j]);
           }
         }
       }
@@ -377,14 +403,14 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p, void
       float a[32], b[32];
       if (MODE == MODE_DGRAD) {
         // dy = dx * (out > 0);  b = dy * xhat
-        const __nv_bfloat16* op = fuse.out + row_off + n0 + col0;
-        const __nv_bfloat16* yp = fuse.y + row_off + n0 + col0;
+        const ET* op = reinterpret_cast<const ET*>(fuse.out) + row_off + n0 + col0;
+        const ET* yp = reinterpret_cast<const ET*>(fuse.y) + row_off + n0 + col0;
 #pragma unroll
         for (int i8 = 0; i8 < 4; ++i8) {
           float o8[8], y8[8];
           if (row_ok) {
-            bf16x8_to_float(*reinterpret_cast<const uint4*>(yp + 8 * i8), y8);
-            if (fuse.relu) bf16x8_to_float(*reinterpret_cast<const uint4*>(op + 8 * i8), o8);
+            load8(yp + 8 * i8, y8);
+            if (fuse.relu) load8(op + 8 * i8, o8);
           }
 #pragma unroll
           for (int j = 0; j < 8; ++j) {

@@ -14,11 +14,12 @@ extern std::atomic<unsigned long long> g_launches;
 constexpr int kMaxClasses = 1024;
 
 // one CTA per sample
+template <typename T>
 __global__ void __launch_bounds__(256)
-head_sample_kernel(const __nv_bfloat16* __restrict__ act, int HW, int C, int classes, const float* __restrict__ fc_w,
+head_sample_kernel(const T* __restrict__ act, int HW, int C, int classes, const float* __restrict__ fc_w,
                    const float* __restrict__ fc_b, const long long* __restrict__ labels, float* __restrict__ pooled,
                    float* __restrict__ logits, float* __restrict__ dlogits, float* __restrict__ loss_n,
-                   float* __restrict__ correct_n, long long* __restrict__ pred, __nv_bfloat16* __restrict__ dact,
+                   float* __restrict__ correct_n, long long* __restrict__ pred, T* __restrict__ dact,
                    int training, float inv_batch) {
   pdl_wait();
   pdl_launch_dependents();
@@ -27,13 +28,14 @@ head_sample_kernel(const __nv_bfloat16* __restrict__ act, int HW, int C, int cla
   float* sl = sm + C;
   float* sd = sl + classes;
   const int n = blockIdx.x;
-  const __nv_bfloat16* a = act + (size_t)n * HW * C;
+  const T* a = act + (size_t)n * HW * C;
   const float inv_hw = 1.f / (float)HW;
   for (int c = threadIdx.x * 2; c < C; c += blockDim.x * 2) {
     float s0 = 0.f, s1 = 0.f;
     for (int p = 0; p < HW; ++p) {
-      const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(a + (size_t)p * C + c));
-      s0 += t.x; s1 += t.y;
+      float t0, t1;
+      load2(a + (size_t)p * C + c, t0, t1);
+      s0 += t0; s1 += t1;
     }
     sp[c] = s0 * inv_hw; sp[c + 1] = s1 * inv_hw;
     pooled[(size_t)n * C + c] = sp[c];
@@ -82,9 +84,7 @@ head_sample_kernel(const __nv_bfloat16* __restrict__ act, int HW, int C, int cla
       const float2 w = *reinterpret_cast<const float2*>(fc_w + (size_t)j * C + c);
       g0 += sd[j] * w.x; g1 += sd[j] * w.y;
     }
-    const __nv_bfloat162 v = __floats2bfloat162_rn(g0 * inv_hw, g1 * inv_hw);
-    for (int p = 0; p < HW; ++p)
-      *reinterpret_cast<__nv_bfloat162*>(dact + ((size_t)n * HW + p) * C + c) = v;
+    for (int p = 0; p < HW; ++p) store2(dact + ((size_t)n * HW + p) * C + c, g0 * inv_hw, g1 * inv_hw);
   }
 }
 
@@ -93,18 +93,20 @@ head_sample_kernel(const __nv_bfloat16* __restrict__ act, int HW, int C, int cla
 // (1.7 ms for ResNet-50 at batch 32).  The wide path keeps the same math but tiles it so that the
 // weight is read once per CTA: pool -> logits (warp per class) -> softmax/CE -> d_act (thread per
 // channel, 8 samples per CTA) -> fc grads (channel tile x class group).
+template <typename T>
 __global__ void __launch_bounds__(256)
-head_pool_kernel(const __nv_bfloat16* __restrict__ act, int HW, int C, float* __restrict__ pooled) {
+head_pool_kernel(const T* __restrict__ act, int HW, int C, float* __restrict__ pooled) {
   pdl_wait();
   pdl_launch_dependents();
   const int n = blockIdx.x;
-  const __nv_bfloat16* a = act + (size_t)n * HW * C;
+  const T* a = act + (size_t)n * HW * C;
   const float inv_hw = 1.f / (float)HW;
   for (int c = threadIdx.x * 2; c < C; c += blockDim.x * 2) {
     float s0 = 0.f, s1 = 0.f;
     for (int p = 0; p < HW; ++p) {
-      const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(a + (size_t)p * C + c));
-      s0 += t.x; s1 += t.y;
+      float t0, t1;
+      load2(a + (size_t)p * C + c, t0, t1);
+      s0 += t0; s1 += t1;
     }
     pooled[(size_t)n * C + c] = s0 * inv_hw;
     pooled[(size_t)n * C + c + 1] = s1 * inv_hw;
@@ -177,8 +179,9 @@ head_softmax_kernel(const float* __restrict__ logits, const long long* __restric
 
 // CTA = (128-channel tile, group of 8 samples); thread = one channel, 8 accumulators; the weight is
 // streamed once per CTA (coalesced over channels), dlogits of the 8 samples are staged in smem.
+template <typename T>
 __global__ void __launch_bounds__(128)
-head_dact_kernel(const float* __restrict__ dlogits, const float* __restrict__ fc_w, __nv_bfloat16* __restrict__ dact,
+head_dact_kernel(const float* __restrict__ dlogits, const float* __restrict__ fc_w, T* __restrict__ dact,
                  int N, int HW, int C, int classes) {
   pdl_wait();
   pdl_launch_dependents();
@@ -202,8 +205,7 @@ head_dact_kernel(const float* __restrict__ dlogits, const float* __restrict__ fc
   }
   const float inv_hw = 1.f / (float)HW;
   for (int i = 0; i < 8 && n0 + i < N; ++i) {
-    const __nv_bfloat16 v = __float2bfloat16(acc[i] * inv_hw);
-    for (int p = 0; p < HW; ++p) dact[((size_t)(n0 + i) * HW + p) * C + c] = v;
+    for (int p = 0; p < HW; ++p) store1(dact + ((size_t)(n0 + i) * HW + p) * C + c, acc[i] * inv_hw);
   }
 }
 
@@ -281,24 +283,25 @@ cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
 
 using namespace ldnn;
 
-extern "C" int ldnn_head_fwd_bwd(const void* act, int N, int HW, int C, int classes, const float* fc_w,
-                                 const float* fc_b, const long long* labels, float* pooled, float* logits,
-                                 float* dlogits, float* loss_n, float* correct_n, long long* pred, void* dact,
-                                 float* dfc_w, float* dfc_b, float* loss_out, float* correct_out, int training,
-                                 void* stream) {
+template <typename T>
+static int head_fwd_bwd_impl(const void* act, int N, int HW, int C, int classes, const float* fc_w,
+                             const float* fc_b, const long long* labels, float* pooled, float* logits,
+                             float* dlogits, float* loss_n, float* correct_n, long long* pred, void* dact,
+                             float* dfc_w, float* dfc_b, float* loss_out, float* correct_out, int training,
+                             void* stream) {
   LDNN_ARG(C % 2 == 0 && classes <= kMaxClasses, "head: C=%d classes=%d", C, classes);
   if (classes > 64) {            // wide head: weight streamed once per CTA instead of once per sample
     cudaStream_t st = (cudaStream_t)stream;
     LDNN_ARG((size_t)8 * classes * sizeof(float) <= 48 * 1024, "head: classes=%d too many for the smem stage", classes);
-    LDNN_CUDA(launch_pdl(head_pool_kernel, dim3(N), dim3(256), 0, st, (const __nv_bfloat16*)act, HW, C, pooled));
+    LDNN_CUDA(launch_pdl(head_pool_kernel<T>, dim3(N), dim3(256), 0, st, (const T*)act, HW, C, pooled));
     LDNN_CUDA(launch_pdl(head_logits_kernel, dim3((classes + 7) / 8), dim3(256), 0, st, (const float*)pooled, fc_w, fc_b,
                          logits, N, C, classes));
     LDNN_CUDA(launch_pdl(head_softmax_kernel, dim3(N), dim3(256), 0, st, (const float*)logits, labels, dlogits, loss_n,
                          correct_n, pred, classes, 1.f / (float)N));
     int launched = 3;
     if (training) {
-      LDNN_CUDA(launch_pdl(head_dact_kernel, dim3((C + 127) / 128, (N + 7) / 8), dim3(128),
-                           (size_t)8 * classes * sizeof(float), st, (const float*)dlogits, fc_w, (__nv_bfloat16*)dact, N,
+      LDNN_CUDA(launch_pdl(head_dact_kernel<T>, dim3((C + 127) / 128, (N + 7) / 8), dim3(128),
+                           (size_t)8 * classes * sizeof(float), st, (const float*)dlogits, fc_w, (T*)dact, N,
                            HW, C, classes));
       ++launched;
     }
@@ -310,9 +313,9 @@ extern "C" int ldnn_head_fwd_bwd(const void* act, int N, int HW, int C, int clas
     return LDNN_OK;
   }
   const size_t smem = (size_t)(C + 2 * classes) * sizeof(float);
-  LDNN_CUDA(launch_pdl(head_sample_kernel, dim3(N), dim3(256), smem, (cudaStream_t)stream, (const __nv_bfloat16*)act, HW,
+  LDNN_CUDA(launch_pdl(head_sample_kernel<T>, dim3(N), dim3(256), smem, (cudaStream_t)stream, (const T*)act, HW,
                        C, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,
-                       (__nv_bfloat16*)dact, training, 1.f / (float)N));
+                       (T*)dact, training, 1.f / (float)N));
   g_launches.fetch_add(1);
   // fc gradients + batch totals on a (channel tile x class group) grid
   LDNN_CUDA(launch_pdl(head_fcgrad_kernel, dim3(training ? (C + 127) / 128 : 1, training ? (classes + 7) / 8 : 1),
@@ -321,6 +324,23 @@ extern "C" int ldnn_head_fwd_bwd(const void* act, int N, int HW, int C, int clas
                        loss_out, correct_out, training));
   g_launches.fetch_add(1);
   return LDNN_OK;
+}
+
+extern "C" int ldnn_head_fwd_bwd(const void* act, int N, int HW, int C, int classes, const float* fc_w,
+                                 const float* fc_b, const long long* labels, float* pooled, float* logits,
+                                 float* dlogits, float* loss_n, float* correct_n, long long* pred, void* dact,
+                                 float* dfc_w, float* dfc_b, float* loss_out, float* correct_out, int training,
+                                 void* stream) {
+  return head_fwd_bwd_impl<__nv_bfloat16>(act, N, HW, C, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n,
+                                          correct_n, pred, dact, dfc_w, dfc_b, loss_out, correct_out, training, stream);
+}
+extern "C" int ldnn_head_fwd_bwd_f32(const void* act, int N, int HW, int C, int classes, const float* fc_w,
+                                     const float* fc_b, const long long* labels, float* pooled, float* logits,
+                                     float* dlogits, float* loss_n, float* correct_n, long long* pred, void* dact,
+                                     float* dfc_w, float* dfc_b, float* loss_out, float* correct_out, int training,
+                                     void* stream) {
+  return head_fwd_bwd_impl<float>(act, N, HW, C, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n,
+                                  correct_n, pred, dact, dfc_w, dfc_b, loss_out, correct_out, training, stream);
 }
 
 extern "C" int ldnn_optim_step(float* params, const float* grads, float* m, float* v, void* shadow_bf16, long long n,

@@ -30,9 +30,9 @@ typedef struct {
   int block_n;         /* 64 / 128 / 256; 0 = auto */
   int splits;          /* split-K factor; 0 = auto */
   int accumulate;      /* dgrad: dx = result + addend */
-  const void* x;       /* bf16 NHWC [N,H,W,Cin]    fprop/wgrad: input;  dgrad: OUTPUT dx */
-  const void* w;       /* bf16 [Cout][R*R*Cin]     (KRSC)                                  */
-  void* y;             /* bf16 NHWC [N,P,Q,Cout]   fprop: OUTPUT; dgrad/wgrad: input dy    */
+  const void* x;       /* bf16|fp32 (see dtype) NHWC [N,H,W,Cin]   fprop/wgrad: input;  dgrad: OUTPUT dx */
+  const void* w;       /* bf16|fp32 [Cout][R*R*Cin]     (KRSC)                                  */
+  void* y;             /* bf16|fp32 NHWC [N,P,Q,Cout]   fprop: OUTPUT; dgrad/wgrad: input dy    */
   void* dw;            /* fp32 [Cout][R*R*Cin]     wgrad: OUTPUT                            */
   const void* addend;  /* dgrad + accumulate: bf16 tensor shaped like dx (may alias x)     */
   float* scratch;      /* split-K partial tiles (see ldnn_conv_query)                      */
@@ -51,6 +51,9 @@ typedef struct {
    * dy = dx * (fuse_out > 0 if fuse_relu).  fuse_out / fuse_y are bf16 tensors shaped like dx. */
   const void* fuse_out; const void* fuse_y; const float* fuse_mean; const float* fuse_invstd; float* fuse_sums;
   int fuse_relu;
+  int dtype;           /* 0: bf16 activations/weights, tcgen05 kind::f16.  1: fp32 activations/weights (x, w, y, addend,
+                          fuse_out, fuse_y are float), tcgen05 kind::tf32 — the reference's precision (fp32 storage,
+                          TF32 convolutions: BalAR/trainer.py:203-210 through model.py:102-111, torch default)   */
 } ldnn_conv_desc;
 
 /* sizes a plan needs; covered_classes (dgrad): how many of the stride^2 output parity classes receive any
@@ -130,6 +133,38 @@ int ldnn_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int
 int ldnn_maxpool_bwd(const void* idx, const void* dy, void* dx, int N, int H, int W, int C, int k, int stride,
                      int pad, void* stream);
 
+/* fp32-storage twins (suffix _f32): the same kernels instantiated for float activations — the BN / pool / stem side
+ * of the TF32 path (ldnn_conv_desc.dtype = 1).  Same arguments; every `void*` activation tensor is float. */
+int ldnn_im2col_stem_f32(const float* x, void* col, int N, int C, int H, int W, int R, int stride, int pad, int Kpad,
+                         void* stream);
+int ldnn_bn_fwd_stats_f32(const void* y, int M, int C, int chunks, float* partial, unsigned int* ticket,
+                          const float* gamma, const float* beta, float* running_mean, float* running_var,
+                          long long* num_batches_tracked, float* save_mean, float* save_invstd, float* scale,
+                          float* shift, float eps, float momentum, void* stream);
+int ldnn_bn_fwd_apply_f32(const void* y, const float* scale, const float* shift, const void* residual, void* out,
+                          int M, int C, int relu, void* stream);
+int ldnn_bn_bwd_reduce_f32(const void* dout, const void* out, const void* y, const float* save_mean,
+                           const float* save_invstd, float* partial, unsigned int* ticket, int M, int C, int chunks,
+                           int relu, float* dgamma, float* dbeta, void* stream);
+int ldnn_bn_bwd_apply_f32(const void* dout, const void* out, const void* y, const float* save_mean,
+                          const float* save_invstd, const float* gamma, const float* dgamma, const float* dbeta,
+                          void* dy_raw, void* dres, int M, int C, int relu, int res_accumulate, void* stream);
+int ldnn_bn_fwd_apply_sums_f32(const void* y, const float* sums, const float* gamma, const float* beta,
+                               float* running_mean, float* running_var, long long* num_batches_tracked,
+                               float* save_mean, float* save_invstd, const void* residual, void* out, int M, int C,
+                               int relu, int training, float eps, float momentum, void* stream);
+int ldnn_bn_bwd_reduce_sums_f32(const void* dout, const void* out, const void* y, const float* save_mean,
+                                const float* save_invstd, float* sums, int M, int C, int chunks, int relu,
+                                void* stream);
+int ldnn_bn_bwd_apply_sums_f32(const void* dout, const void* out, const void* y, const float* save_mean,
+                               const float* save_invstd, const float* gamma, const float* sums, void* dy_raw,
+                               void* dres, float* dgamma, float* dbeta, int M, int C, int relu, int res_accumulate,
+                               void* stream);
+int ldnn_maxpool_fwd_f32(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride, int pad,
+                         void* stream);
+int ldnn_maxpool_bwd_f32(const void* idx, const void* dy, void* dx, int N, int H, int W, int C, int k, int stride,
+                         int pad, void* stream);
+
 /* ------------------------------------------------------------------ head (K-HEAD)
  * global-avg-pool + linear + softmax cross-entropy (+ correct count, dlogits, d_act, fc grads)
  * (model.py:99-100,108-110; main.py:52; trainer.py:207,212-216). */
@@ -139,6 +174,12 @@ int ldnn_head_fwd_bwd(const void* act /* bf16 [N][HW][C] */, int N, int HW, int 
                       float* correct_n /* [N] */, long long* pred /* [N] */, void* dact /* bf16 like act */,
                       float* dfc_w, float* dfc_b, float* loss_out /* mean loss */, float* correct_out /* count */,
                       int training, void* stream);
+
+/* float activations (TF32 path) */
+int ldnn_head_fwd_bwd_f32(const void* act, int N, int HW, int C, int classes, const float* fc_w, const float* fc_b,
+                          const long long* labels, float* pooled, float* logits, float* dlogits, float* loss_n,
+                          float* correct_n, long long* pred, void* dact, float* dfc_w, float* dfc_b, float* loss_out,
+                          float* correct_out, int training, void* stream);
 
 /* ------------------------------------------------------------------ optimizer (K-OPT)
  * Adam / SGD-momentum on flat fp32 slabs, also emits the bf16 compute copy
@@ -174,6 +215,9 @@ typedef struct {
   unsigned long long timeout_cycles;   /* spin-wait watchdog; 0 = default */
   void* signal[LDNN_MAX_RANKS];        /* per-rank signal pad (uint32[LDNN_SIGNAL_WORDS]) */
   int* error_flag;                     /* set to nonzero on watchdog expiry (local) */
+  int debug_delay_block;               /* tests: CTA (this - 1) of every rank idles debug_delay_cycles before it
+                                          pushes (0 = off); exposes cross-CTA ordering assumptions            */
+  unsigned int debug_delay_cycles;
 } ldnn_comm;
 #define LDNN_SIGNAL_WORDS 65536
 

@@ -55,7 +55,8 @@ class Config:
     weight_decay: float = 0.0
     lr_step: int = 25
     lr_gamma: float = 0.1
-    dtype: str = "bf16"                      # compute dtype on GPU; CPU path is fp32
+    dtype: str = "tf32"                      # GPU compute: tf32 (fp32 storage + TF32 MMA = the reference's
+                                             # numerics, default) | bf16 (native, faster) | fp32 (torch engine)
     apply_exchanged_grads: Optional[bool] = None  # None → product=True, compat(global_epoch)=False
     synthetic: bool = False
     synthetic_train: int = 4096
@@ -117,7 +118,7 @@ def build_parser(topology: Optional[str] = None, balance: Optional[str] = None) 
     p.add_argument("--weight_decay", type=float, default=d.weight_decay)
     p.add_argument("--lr_step", type=int, default=d.lr_step)
     p.add_argument("--lr_gamma", type=float, default=d.lr_gamma)
-    p.add_argument("--dtype", choices=["bf16", "fp32"], default=d.dtype)
+    p.add_argument("--dtype", choices=["tf32", "bf16", "fp32"], default=d.dtype)
     p.add_argument("--apply_exchanged_grads", type=lambda s: s.lower() in ("1", "true", "yes"), default=None)
     p.add_argument("--synthetic", action="store_true")
     p.add_argument("--synthetic_train", type=int, default=d.synthetic_train)

@@ -256,20 +256,20 @@ def make_engine(cfg, rt) -> Engine:
         kw["widths"] = (8, 16, 32, 64, 128)      # test-only: same topology, 1/64 of the FLOPs
     spec = get_spec(cfg.model, **kw)
     kind = cfg.engine
-    dtype = getattr(cfg, "dtype", "bf16")
+    dtype = getattr(cfg, "dtype", "tf32")
     if kind == "auto":
-        # the sm_100a kernels compute in bf16 (fp32 master weights, fp32 accumulation); --dtype fp32 selects
-        # the torch engine (fp32 model on the same flat slabs, same exchange)
-        kind = "native" if (rt.is_cuda and dtype == "bf16") else "torch"
+        # the sm_100a kernels compute in tf32 (fp32 storage, TF32 tensor-core MMA: the reference's numerics) or
+        # bf16 (bf16 storage, fp32 master weights); --dtype fp32 selects the torch engine (same flat slabs)
+        kind = "native" if (rt.is_cuda and dtype in ("tf32", "bf16")) else "torch"
     if kind == "native":
         if not rt.is_cuda:
             raise RuntimeError("--engine native needs a CUDA device (sm_100a)")
-        if dtype != "bf16":
-            raise RuntimeError("--engine native computes in bf16 with fp32 master weights; use --engine torch "
-                               "(or auto) with --dtype fp32")
+        if dtype not in ("tf32", "bf16"):
+            raise RuntimeError("--engine native computes in tf32 or bf16 (fp32 accumulation, fp32 master weights); "
+                               "use --engine torch (or auto) with --dtype fp32")
         from .models.native import NativeEngine
         # rings are latency-bound per launch: fewer, larger buckets for the overlapped per-step exchange
         bucket_mb = 64 if (cfg.sync == "step" and cfg.topology != "allreduce") else 32
         return NativeEngine(spec, rt.device, opt, batch_size=cfg.batch_size, world_size=rt.world_size,
-                            rank=rt.rank, bucket_mb=bucket_mb)
+                            rank=rt.rank, bucket_mb=bucket_mb, dtype=dtype)
     return TorchEngine(spec, rt.device, opt)

@@ -3,8 +3,11 @@
 What torch autograd + cuDNN do for the reference (``trainer.py:205-210`` through
 ``model.py:102-111``) is done here by an explicit plan:
 
-* all buffers are allocated once (activations NHWC bf16, flat fp32 params/grads/moments
-  in IPC-shareable memory, bf16 compute copy of the weights in KRSC order);
+* all buffers are allocated once (activations NHWC, flat fp32 params/grads/moments
+  in IPC-shareable memory, weights in KRSC order);
+* two precisions (``dtype``): ``"tf32"`` — fp32 activations and the fp32 master weights fed straight to
+  ``tcgen05.mma kind::tf32`` (the reference's own numerics: fp32 storage + TF32 convolutions, no shadow
+  copy, no cast) — and ``"bf16"`` — bf16 activations and a bf16 compute copy of the weights (``kind::f16``);
 * forward = per unit ``conv_fprop → bn_stats → bn_apply(+residual,+relu)``, head =
   ``pool+fc+CE (+dlogits, d_act, fc grads)``; backward walks the units in reverse:
   ``bn_bwd_reduce → bn_bwd_apply → conv_wgrad (→ flat grad slab) → conv_dgrad``;
@@ -54,7 +57,13 @@ class NativeEngine(Engine):
     permuted_layout = True
 
     def __init__(self, spec: NetSpec, device, opt: OptimConfig, batch_size: int = 64, world_size: int = 1,
-                 rank: int = 0, init: bool = True, use_graph: bool = True, bucket_mb: Optional[int] = None):
+                 rank: int = 0, init: bool = True, use_graph: bool = True, bucket_mb: Optional[int] = None,
+                 dtype: str = "tf32"):
+        if dtype not in ("tf32", "bf16"):
+            raise ValueError(f"NativeEngine dtype must be 'tf32' or 'bf16', got {dtype!r}")
+        self.dtype = dtype
+        self.act_dtype = torch.float32 if dtype == "tf32" else torch.bfloat16
+        self.dcode = 1 if dtype == "tf32" else 0          # ldnn_conv_desc.dtype
         if not L.available():
             raise L.LdnnError("libldnn_b200.so is not built; run `python -m ldnn_b200.build`")
         self.spec, self.device, self.max_batch = spec, canonical_device(device), batch_size
@@ -96,7 +105,8 @@ class NativeEngine(Engine):
             off += (n + ALIGN - 1) // ALIGN * ALIGN
         self._symm = {}          # name -> (tensor, ipc handle, raw ptr)
         self.flat = FlatState(slots, off, self.device, opt, allocator=self._alloc_flat)
-        self.shadow = torch.zeros(off, dtype=torch.bfloat16, device=self.device)   # bf16 compute copy
+        # bf16 compute copy of the weights; the tf32 path reads the fp32 master slab directly
+        self.shadow = torch.zeros(off, dtype=torch.bfloat16, device=self.device) if dtype == "bf16" else None
         # ---- BN buffers -------------------------------------------------------------
         self.bn_off: Dict[str, int] = {}
         c_tot = 0
@@ -199,7 +209,8 @@ class NativeEngine(Engine):
         self.params_changed()
 
     def params_changed(self) -> None:
-        K.cast_bf16(self.flat.params, self.shadow, self.flat.total)
+        if self.shadow is not None:
+            K.cast_bf16(self.flat.params, self.shadow, self.flat.total)
 
     # ------------------------------------------------------------------ steps
     def _plan(self, n: int, training: bool) -> "_StepPlan":
@@ -235,7 +246,7 @@ class NativeEngine(Engine):
             opt_stream.wait_event(ev)
             with torch.cuda.stream(opt_stream):
                 K.optim_step(f.params[lo:hi], f.grads[lo:hi], f.m[lo:hi], None if f.v is None else f.v[lo:hi],
-                             self.shadow[lo:hi], hi - lo, o)
+                             None if self.shadow is None else self.shadow[lo:hi], hi - lo, o)
 
         p.run_bucketed(x, y, on_bucket)
         ev = torch.cuda.Event()
@@ -257,7 +268,7 @@ class NativeEngine(Engine):
         f = self.flat
         f.step += 1
         o = L.make_optim(f.opt, f.step, f.lr)
-        K.optim_step(f.params, f.grads, f.m, f.v, self.shadow, f.total, o)
+        K.optim_step(f.params, f.grads, f.m, f.v, self.shadow, f.total, o)     # shadow None (tf32): no cast
 
     @torch.no_grad()
     def eval_step(self, x, y):
@@ -275,7 +286,7 @@ class _StepPlan:
     def __init__(self, eng: NativeEngine, n: int, training: bool):
         self.eng, self.n, self.training = eng, n, training
         dev, spec = eng.device, eng.spec
-        bf = lambda *shape: torch.zeros(*shape, dtype=torch.bfloat16, device=dev)
+        bf = lambda *shape: torch.zeros(*shape, dtype=eng.act_dtype, device=dev)     # activation storage type
         f32 = lambda *shape: torch.zeros(*shape, dtype=torch.float32, device=dev)
         H0, W0, C0 = eng.slot_shape["x"]
         self.x_in = f32(n, C0, H0, W0)
@@ -328,8 +339,9 @@ class _StepPlan:
     def _build(self):
         eng, n, spec = self.eng, self.n, self.eng.spec
         fl = eng.flat
-        W = lambda key: eng.shadow[fl.by_key[key].offset:fl.by_key[key].offset + fl.by_key[key].numel]
         P = lambda key: fl.params[fl.by_key[key].offset:fl.by_key[key].offset + fl.by_key[key].numel]
+        W = P if eng.shadow is None else (                 # conv weights as the MMA reads them
+            lambda key: eng.shadow[fl.by_key[key].offset:fl.by_key[key].offset + fl.by_key[key].numel])
         G = lambda key: fl.grads[fl.by_key[key].offset:fl.by_key[key].offset + fl.by_key[key].numel]
         dev = eng.device
         # ---- first pass: size the shared split-K workspace ----
@@ -346,13 +358,13 @@ class _StepPlan:
         atomic = not eng.deterministic
         need = 0
         for m, g in descs:
-            need = max(need, K.conv_query(m, *g, atomic_out=(atomic and m == K.WGRAD))[0])
+            need = max(need, K.conv_query(m, *g, atomic_out=(atomic and m == K.WGRAD), dtype=eng.dcode)[0])
             if eng.autotune:                        # the tuner may pick any candidate: size for the largest
                 n_total = g[4] if m == K.FPROP else g[3]
                 for bn, sp in K.conv_candidates(m, g, n_total):
                     try:
                         need = max(need, K.conv_query(m, *g, block_n=bn, splits=sp,
-                                                      atomic_out=(atomic and m == K.WGRAD))[0])
+                                                      atomic_out=(atomic and m == K.WGRAD), dtype=eng.dcode)[0])
                     except L.LdnnError:
                         pass
         ws.reserve(min(need, 1 << 30))
@@ -483,7 +495,7 @@ class _StepPlan:
             geo, xin = (n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad), self.act[u.src]
         bn_, sp_, lt_ = K.tuned_conv_config(
             K.FPROP, geo, lambda b, s_, l_: K.ConvPlan(K.FPROP, *geo, xin, w, yraw, bn_sums=fsum, block_n=b, splits=s_,
-                                                       lite=l_), eng.autotune)
+                                                       lite=l_), eng.autotune, eng.dcode)
         plan = K.ConvPlan(K.FPROP, *geo, xin, w, yraw, workspace=self.ws, bn_sums=fsum, block_n=bn_, splits=sp_,
                           lite=lt_)
         self._add(plan.run, plan.num_launches)
@@ -538,10 +550,11 @@ class _StepPlan:
         atomic = not eng.deterministic
         bn_, sp_, lt_ = K.tuned_conv_config(
             K.WGRAD, geo, lambda b, s_, l_: K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, atomic_out=atomic,
-                                                       block_n=b, splits=s_, lite=l_), eng.autotune and atomic)
+                                                       block_n=b, splits=s_, lite=l_), eng.autotune and atomic,
+            eng.dcode)
         wg = K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, workspace=self.ws, atomic_out=atomic, block_n=bn_,
                         splits=sp_, lite=lt_)
-        if atomic and K.conv_query(K.WGRAD, *geo, block_n=bn_, splits=sp_)[0] > 0:   # split-K → red.add into a zeroed slice
+        if atomic and K.conv_query(K.WGRAD, *geo, block_n=bn_, splits=sp_, dtype=eng.dcode)[0] > 0:   # split-K → red.add into a zeroed slice
             sl = eng.flat.by_key[u.conv_key + ".weight"]
             self.zero_ranges.append((sl.offset, sl.offset + sl.numel))
         self._add(wg.run, wg.num_launches, side=True)
@@ -550,13 +563,13 @@ class _StepPlan:
         dx = self.dact[u.src]
         acc = u.src in written
         # strided 1x1 dgrads leave parity classes untouched: start from zero and accumulate
-        full_cover = K.conv_query(K.DGRAD, *geo, accumulate=True)[3] == u.stride * u.stride
+        full_cover = K.conv_query(K.DGRAD, *geo, accumulate=True, dtype=eng.dcode)[3] == u.stride * u.stride
         if not acc and not full_cover:
             self._add(lambda: dx.zero_(), 0)
             acc = True
         bn_, sp_, lt_ = K.tuned_conv_config(
             K.DGRAD, geo, lambda b, s_, l_: K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx, accumulate=True, block_n=b,
-                                                       splits=s_, lite=l_), eng.autotune)
+                                                       splits=s_, lite=l_), eng.autotune, eng.dcode)
         fuse = None
         if u.conv_key in self.fuse_into:
             ow = self.fuse_into[u.conv_key]

@@ -33,7 +33,7 @@ class ConvDesc(C.Structure):
                 ("tickets", C.c_void_p), ("a_lbo", C.c_uint), ("a_sbo", C.c_uint), ("b_lbo", C.c_uint),
                 ("b_sbo", C.c_uint), ("cluster", C.c_int), ("lite", C.c_int), ("atomic_out", C.c_int), ("bn_sums", C.c_void_p), ("fuse_out", C.c_void_p), ("fuse_y", C.c_void_p),
                 ("fuse_mean", C.c_void_p), ("fuse_invstd", C.c_void_p), ("fuse_sums", C.c_void_p),
-                ("fuse_relu", C.c_int)]
+                ("fuse_relu", C.c_int), ("dtype", C.c_int)]
 
 
 class Optim(C.Structure):
@@ -45,7 +45,7 @@ class Optim(C.Structure):
 class Comm(C.Structure):
     _fields_ = [("rank", C.c_int), ("world", C.c_int), ("emulate", C.c_int), ("blocks", C.c_int),
                 ("epoch", C.c_uint), ("timeout_cycles", C.c_ulonglong), ("signal", C.c_void_p * MAX_RANKS),
-                ("error_flag", C.c_void_p)]
+                ("error_flag", C.c_void_p), ("debug_delay_block", C.c_int), ("debug_delay_cycles", C.c_uint)]
 
 
 class Exchange(C.Structure):

@@ -18,6 +18,16 @@ from . import _lib as L
 FPROP, DGRAD, WGRAD = 0, 1, 2
 
 
+def _fn(name: str, t: torch.Tensor):
+    """Entry point for the storage type of activation tensor `t`: bf16 = `ldnn_<name>`, fp32 (the TF32
+    path, conv desc dtype 1) = `ldnn_<name>_f32`."""
+    if t.dtype == torch.float32:
+        return getattr(L.lib(), f"ldnn_{name}_f32")
+    if t.dtype != torch.bfloat16:
+        raise L.LdnnError(f"{name}: activations must be bfloat16 or float32, got {t.dtype}")
+    return getattr(L.lib(), f"ldnn_{name}")
+
+
 class ConvPlan:
     """A bound, reusable convolution launch (tensor maps + tiling + split-K workspace).
     Pointers are baked in — the static-graph executor owns fixed buffers."""
@@ -38,6 +48,7 @@ class ConvPlan:
         d.atomic_out = int(atomic_out)
         d.cluster = int(cluster)
         d.lite = int(lite)
+        d.dtype = 1 if x.dtype == torch.float32 else 0      # fp32 storage -> tcgen05 kind::tf32
         if bn_bwd_fuse is not None:        # (out, y, mean, invstd, sums, relu) of the layer that owns dx
             f_out, f_y, f_mean, f_is, f_sums, f_relu = bn_bwd_fuse
             d.fuse_out, d.fuse_y, d.fuse_mean = f_out.data_ptr(), f_y.data_ptr(), f_mean.data_ptr()
@@ -79,6 +90,10 @@ class ConvPlan:
 # tiling depends on how many CTAs it yields — measured once per shape at plan-build time.
 _TUNE_CACHE = {}
 _TUNE_FILE_LOADED = False
+# Tuned (block_n, splits, lite) for the shapes of the shipped models at batch 64, measured on B200
+# (bf16 and tf32): loaded before anything else so a fresh process does not re-time ~70 candidate plans
+# per layer; only shapes that are in neither this file nor $LDNN_TUNE_CACHE are tuned at plan build.
+DEFAULT_TUNE_FILE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tuned_defaults.json")
 
 
 def _tune_file():
@@ -106,6 +121,8 @@ def load_tune_cache(path=None):
     for ks, cfg in blob.get("configs", {}).items():
         try:
             key = tuple(int(v) for v in ks.split(","))
+            if len(key) == 9:                     # round-1 files: (mode, geometry) of the bf16 kernels
+                key = (0,) + key
             _TUNE_CACHE.setdefault(key, (int(cfg[0]), int(cfg[1]), bool(cfg[2])))
             n += 1
         except (ValueError, IndexError, TypeError):
@@ -118,7 +135,7 @@ def save_tune_cache(path=None):
     path = path or _tune_file()
     if not path:
         return False
-    blob = {"version": 1, "configs": {_tune_key_str(k): [c[0], c[1], bool(c[2])] for k, c in sorted(_TUNE_CACHE.items())}}
+    blob = {"version": 2, "key": "dtype(0 bf16, 1 tf32),mode,N,H,W,Cin,Cout,R,stride,pad", "configs": {_tune_key_str(k): [c[0], c[1], bool(c[2])] for k, c in sorted(_TUNE_CACHE.items())}}
     tmp = f"{path}.{os.getpid()}.tmp"
     try:
         with open(tmp, "w") as f:
@@ -155,17 +172,19 @@ def conv_candidates(mode, geo, n_total):
     return out
 
 
-def tuned_conv_config(mode, geo, make_plan, enabled=True):
+def tuned_conv_config(mode, geo, make_plan, enabled=True, dtype=0):
     """Returns (block_n, splits, lite) — (0, 0, False) = library heuristics.  `make_plan(block_n,
     splits, lite)` must build a runnable plan (private scratch) for timing.  `lite` (two CTAs per SM)
-    is tried only for grids of more than one wave."""
+    is tried only for grids of more than one wave.  `dtype`: 0 bf16, 1 tf32 (separate tunings)."""
     global _TUNE_FILE_LOADED
-    key = (int(mode),) + tuple(int(v) for v in geo)
+    key = (int(dtype), int(mode)) + tuple(int(v) for v in geo)
     if not _TUNE_FILE_LOADED:
         _TUNE_FILE_LOADED = True
-        load_tune_cache()
-    if not enabled:                                # no timing runs; a tuning file, if given, is still replayed
-        return _TUNE_CACHE[key] if (_tune_file() and key in _TUNE_CACHE) else (0, 0, False)
+        load_tune_cache()                          # $LDNN_TUNE_CACHE first: it overrides the shipped defaults
+        if not os.environ.get("LDNN_NO_TUNE_DEFAULTS"):
+            load_tune_cache(DEFAULT_TUNE_FILE)
+    if not enabled:                                # no timing runs; known tunings are still replayed
+        return _TUNE_CACHE.get(key, (0, 0, False))
     if key in _TUNE_CACHE:
         return _TUNE_CACHE[key]
     N, H, W, Cin, Cout, R, stride, pad = geo
@@ -217,9 +236,11 @@ class Workspace:
         self.scratch = torch.empty(max(self.need // 4, 1), dtype=torch.float32, device=self.device)
 
 
-def conv_query(mode, N, H, W, Cin, Cout, R, stride, pad, block_n=0, splits=0, accumulate=True, atomic_out=False):
+def conv_query(mode, N, H, W, Cin, Cout, R, stride, pad, block_n=0, splits=0, accumulate=True, atomic_out=False,
+               dtype=0):
     """(scratch bytes, ticket count, launches, covered dgrad parity classes)."""
     d = L.ConvDesc()
+    d.dtype = int(dtype)
     d.mode, d.N, d.H, d.W, d.Cin, d.Cout, d.R, d.stride, d.pad = mode, N, H, W, Cin, Cout, R, stride, pad
     d.block_n, d.splits, d.accumulate, d.atomic_out = block_n, splits, int(accumulate), int(atomic_out)
     sb, tk, nl, cc = C.c_size_t(0), C.c_size_t(0), C.c_int(0), C.c_int(0)
@@ -228,13 +249,13 @@ def conv_query(mode, N, H, W, Cin, Cout, R, stride, pad, block_n=0, splits=0, ac
 
 
 def im2col_stem(x_nchw_f32, col_bf16, N, Cc, H, W, R, stride, pad, Kpad):
-    L.check(L.lib().ldnn_im2col_stem(L.ptr(x_nchw_f32), L.ptr(col_bf16), N, Cc, H, W, R, stride, pad, Kpad,
+    L.check(_fn("im2col_stem", col_bf16)(L.ptr(x_nchw_f32), L.ptr(col_bf16), N, Cc, H, W, R, stride, pad, Kpad,
                                      L.stream_ptr()))
 
 
 def bn_fwd_stats(y, M, Cc, chunks, partial, ticket, gamma, beta, rmean, rvar, nbt, save_mean, save_invstd, scale,
                  shift, eps=1e-5, momentum=0.1):
-    L.check(L.lib().ldnn_bn_fwd_stats(L.ptr(y), M, Cc, chunks, L.ptr(partial), L.ptr(ticket), L.ptr(gamma),
+    L.check(_fn("bn_fwd_stats", y)(L.ptr(y), M, Cc, chunks, L.ptr(partial), L.ptr(ticket), L.ptr(gamma),
                                       L.ptr(beta), L.ptr(rmean), L.ptr(rvar), L.ptr(nbt), L.ptr(save_mean),
                                       L.ptr(save_invstd), L.ptr(scale), L.ptr(shift), C.c_float(eps),
                                       C.c_float(momentum), L.stream_ptr()))
@@ -246,54 +267,54 @@ def bn_eval_coeffs(gamma, beta, rmean, rvar, scale, shift, Cc, eps=1e-5):
 
 
 def bn_fwd_apply(y, scale, shift, residual, out, M, Cc, relu):
-    L.check(L.lib().ldnn_bn_fwd_apply(L.ptr(y), L.ptr(scale), L.ptr(shift), L.ptr(residual), L.ptr(out), M, Cc,
+    L.check(_fn("bn_fwd_apply", y)(L.ptr(y), L.ptr(scale), L.ptr(shift), L.ptr(residual), L.ptr(out), M, Cc,
                                       int(relu), L.stream_ptr()))
 
 
 def bn_bwd_reduce(dout, out, y, save_mean, save_invstd, partial, ticket, M, Cc, chunks, relu, dgamma, dbeta):
-    L.check(L.lib().ldnn_bn_bwd_reduce(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
+    L.check(_fn("bn_bwd_reduce", y)(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
                                        L.ptr(partial), L.ptr(ticket), M, Cc, chunks, int(relu), L.ptr(dgamma),
                                        L.ptr(dbeta), L.stream_ptr()))
 
 
 def bn_bwd_apply(dout, out, y, save_mean, save_invstd, gamma, dgamma, dbeta, dy_raw, dres, M, Cc, relu,
                  res_accumulate):
-    L.check(L.lib().ldnn_bn_bwd_apply(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
+    L.check(_fn("bn_bwd_apply", y)(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
                                       L.ptr(gamma), L.ptr(dgamma), L.ptr(dbeta), L.ptr(dy_raw), L.ptr(dres), M, Cc,
                                       int(relu), int(res_accumulate), L.stream_ptr()))
 
 
 def bn_fwd_apply_sums(y, sums, gamma, beta, rmean, rvar, nbt, save_mean, save_invstd, residual, out, M, Cc, relu,
                       training, eps=1e-5, momentum=0.1):
-    L.check(L.lib().ldnn_bn_fwd_apply_sums(L.ptr(y), L.ptr(sums), L.ptr(gamma), L.ptr(beta), L.ptr(rmean), L.ptr(rvar),
+    L.check(_fn("bn_fwd_apply_sums", y)(L.ptr(y), L.ptr(sums), L.ptr(gamma), L.ptr(beta), L.ptr(rmean), L.ptr(rvar),
                                            L.ptr(nbt), L.ptr(save_mean), L.ptr(save_invstd), L.ptr(residual),
                                            L.ptr(out), M, Cc, int(relu), int(training), C.c_float(eps),
                                            C.c_float(momentum), L.stream_ptr()))
 
 
 def bn_bwd_reduce_sums(dout, out, y, save_mean, save_invstd, sums, M, Cc, chunks, relu):
-    L.check(L.lib().ldnn_bn_bwd_reduce_sums(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
+    L.check(_fn("bn_bwd_reduce_sums", y)(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
                                             L.ptr(sums), M, Cc, chunks, int(relu), L.stream_ptr()))
 
 
 def bn_bwd_apply_sums(dout, out, y, save_mean, save_invstd, gamma, sums, dy_raw, dres, dgamma, dbeta, M, Cc, relu,
                       res_accumulate):
-    L.check(L.lib().ldnn_bn_bwd_apply_sums(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
+    L.check(_fn("bn_bwd_apply_sums", y)(L.ptr(dout), L.ptr(out), L.ptr(y), L.ptr(save_mean), L.ptr(save_invstd),
                                            L.ptr(gamma), L.ptr(sums), L.ptr(dy_raw), L.ptr(dres), L.ptr(dgamma),
                                            L.ptr(dbeta), M, Cc, int(relu), int(res_accumulate), L.stream_ptr()))
 
 
 def maxpool_fwd(x, y, idx, N, H, W, Cc, k, stride, pad):
-    L.check(L.lib().ldnn_maxpool_fwd(L.ptr(x), L.ptr(y), L.ptr(idx), N, H, W, Cc, k, stride, pad, L.stream_ptr()))
+    L.check(_fn("maxpool_fwd", x)(L.ptr(x), L.ptr(y), L.ptr(idx), N, H, W, Cc, k, stride, pad, L.stream_ptr()))
 
 
 def maxpool_bwd(idx, dy, dx, N, H, W, Cc, k, stride, pad):
-    L.check(L.lib().ldnn_maxpool_bwd(L.ptr(idx), L.ptr(dy), L.ptr(dx), N, H, W, Cc, k, stride, pad, L.stream_ptr()))
+    L.check(_fn("maxpool_bwd", dy)(L.ptr(idx), L.ptr(dy), L.ptr(dx), N, H, W, Cc, k, stride, pad, L.stream_ptr()))
 
 
 def head_fwd_bwd(act, N, HW, Cc, classes, fc_w, fc_b, labels, pooled, logits, dlogits, loss_n, correct_n, pred,
                  dact, dfc_w, dfc_b, loss_out, correct_out, training):
-    L.check(L.lib().ldnn_head_fwd_bwd(L.ptr(act), N, HW, Cc, classes, L.ptr(fc_w), L.ptr(fc_b), L.ptr(labels),
+    L.check(_fn("head_fwd_bwd", act)(L.ptr(act), N, HW, Cc, classes, L.ptr(fc_w), L.ptr(fc_b), L.ptr(labels),
                                       L.ptr(pooled), L.ptr(logits), L.ptr(dlogits), L.ptr(loss_n), L.ptr(correct_n),
                                       L.ptr(pred), L.ptr(dact), L.ptr(dfc_w), L.ptr(dfc_b), L.ptr(loss_out),
                                       L.ptr(correct_out), int(training), L.stream_ptr()))

@@ -8,12 +8,18 @@ def fp32_mode():
     torch.backends.cuda.matmul.allow_tf32 = False
 
 
-def make_conv_case(N, H, W, Cin, Cout, R, stride, pad, seed=0, dev="cuda"):
+# element types of the native conv: bf16 storage (kind::f16) and fp32 storage (kind::tf32), with the max-rel
+# tolerances of the output against an fp32 cuDNN reference with TF32 off: (activations, weight gradient)
+DTYPES = {"bf16": torch.bfloat16, "tf32": torch.float32}
+TOL = {"bf16": (1.5e-2, 5e-3), "tf32": (2e-3, 2e-3)}
+
+
+def make_conv_case(N, H, W, Cin, Cout, R, stride, pad, seed=0, dev="cuda", dtype=torch.bfloat16):
     g = torch.Generator(device="cpu").manual_seed(seed)
     P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
-    x = (torch.randn(N, H, W, Cin, generator=g) * 0.5).to(dev).bfloat16()
-    w = (torch.randn(Cout, R, R, Cin, generator=g) / (R * R * Cin) ** 0.5).to(dev).bfloat16()
-    dy = (torch.randn(N, P, Q, Cout, generator=g) * 0.5).to(dev).bfloat16()
+    x = (torch.randn(N, H, W, Cin, generator=g) * 0.5).to(dev).to(dtype)
+    w = (torch.randn(Cout, R, R, Cin, generator=g) / (R * R * Cin) ** 0.5).to(dev).to(dtype)
+    dy = (torch.randn(N, P, Q, Cout, generator=g) * 0.5).to(dev).to(dtype)
     return x, w, dy, P, Q
 
 

@@ -87,20 +87,29 @@ def test_tune_cache_roundtrip_and_replay(tmp_path, monkeypatch):
     monkeypatch.setattr(K, "_TUNE_CACHE", {})
     monkeypatch.setattr(K, "_TUNE_FILE_LOADED", False)
     geo = (64, 32, 32, 64, 128, 3, 1, 1)
-    K._TUNE_CACHE[(K.FPROP,) + geo] = (128, 2, True)
-    K._TUNE_CACHE[(K.WGRAD,) + geo] = (0, 0, False)
+    # keys are (dtype, mode, geometry): dtype 0 = bf16 kernels, 1 = tf32 kernels (tuned separately)
+    K._TUNE_CACHE[(0, K.FPROP) + geo] = (128, 2, True)
+    K._TUNE_CACHE[(1, K.FPROP) + geo] = (64, 3, False)
+    K._TUNE_CACHE[(0, K.WGRAD) + geo] = (0, 0, False)
     assert K.save_tune_cache()
     monkeypatch.setattr(K, "_TUNE_CACHE", {})
-    assert K.load_tune_cache() == 2
-    assert K._TUNE_CACHE[(K.FPROP,) + geo] == (128, 2, True)
-    # timing disabled + file given: cached choice is replayed, unknown shapes fall back to heuristics;
+    assert K.load_tune_cache() == 3
+    assert K._TUNE_CACHE[(0, K.FPROP) + geo] == (128, 2, True)
+    # timing disabled: known choices are replayed per dtype, unknown shapes fall back to heuristics;
     # make_plan must never be called on this path (no GPU here)
+    monkeypatch.setenv("LDNN_NO_TUNE_DEFAULTS", "1")
     boom = lambda *a: (_ for _ in ()).throw(AssertionError("timed"))
     assert K.tuned_conv_config(K.FPROP, geo, boom, enabled=False) == (128, 2, True)
+    assert K.tuned_conv_config(K.FPROP, geo, boom, enabled=False, dtype=1) == (64, 3, False)
     assert K.tuned_conv_config(K.DGRAD, geo, boom, enabled=False) == (0, 0, False)
-    # without a file, disabled means heuristics even if the process cache has an entry
-    monkeypatch.delenv("LDNN_TUNE_CACHE")
-    assert K.tuned_conv_config(K.FPROP, geo, boom, enabled=False) == (0, 0, False)
+    # a round-1 file (9-int keys, bf16 kernels only) still loads, as dtype 0
+    old = tmp_path / "old.json"
+    old.write_text('{"version": 1, "configs": {"1,64,32,32,64,128,3,1,1": [64, 4, false]}}')
+    assert K.load_tune_cache(str(old)) == 1
+    assert K._TUNE_CACHE[(0, K.DGRAD) + geo] == (64, 4, False)
+    # the shipped defaults cover the repo model's shapes at batch 64, so a fresh process does not re-time them
+    monkeypatch.setattr(K, "_TUNE_CACHE", {})
+    assert K.load_tune_cache(K.DEFAULT_TUNE_FILE) > 0
     # a corrupt file is ignored
     path.write_text("{not json")
     assert K.load_tune_cache(str(path)) == 0

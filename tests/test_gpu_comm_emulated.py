@@ -205,3 +205,55 @@ def test_watchdog_reports_a_missing_peer():
     L.check(L.lib().ldnn_barrier(C.byref(c), None))
     torch.cuda.synchronize()
     assert int(emu.err.item()) == 1
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("variant", ["selfmix", "update_cast", "nvls_update_cast"])
+def test_two_shot_tail_reads_only_what_its_own_barrier_covers(world, variant):
+    """The barrier before the two-shot kernels' local tail joins CTA b of this rank with CTA b of each peer only.
+    One CTA index of every rank is held back (~1 ms) before it pushes: a tail that walked the slab with another
+    element-to-CTA mapping than the pushes would read slices the late CTA has not delivered yet (stale self-mix
+    sums, stale bf16 shadow).  Results must be unaffected by the delay."""
+    from ldnn_b200.engine import OptimConfig
+    from ldnn_b200.ops import _lib as L
+    n = 4 * 70_003
+    blocks = 6
+    opt = OptimConfig(kind="adam", lr=1e-2)
+    outs = []
+    for delay_block in (0, 3):
+        emu = Emu(world, n, blocks=blocks)
+        grads = _data(world, n, seed=5)
+        p0 = torch.randn(n, generator=torch.Generator().manual_seed(9)).cuda()
+        params = [p0.clone() for _ in range(world)]
+        recv = [torch.full((n,), 7.0).cuda() for _ in range(world)]       # stale staging content
+        m, v = torch.zeros(n).cuda(), torch.zeros(n).cuda()
+        shadow = torch.full((n,), -3.0, dtype=torch.bfloat16).cuda()      # stale shadow content
+        e = L.Exchange()
+        gt, pt, rt_ = emu.table(grads), emu.table(params), emu.table(recv)
+        for i in range(L.MAX_RANKS):
+            e.grads[i], e.params[i], e.recv[i] = gt[i], pt[i], rt_[i]
+        e.n = n
+        c = emu.comm()
+        c.debug_delay_block, c.debug_delay_cycles = delay_block + (1 if delay_block else 0), 2_000_000
+        if variant == "selfmix":
+            e.mode, e.self_coef = L.X_SELFMIX, 0.7
+            for i in range(world):
+                e.weight[i] = 0.3 / max(world - 1, 1)
+            L.check(L.lib().ldnn_allreduce_fused(C.byref(c), C.byref(e), None))
+            emu.ok()
+            outs.append(torch.stack(grads).clone())
+        else:
+            e.mode = L.X_UPDATE
+            e.m, e.v, e.shadow = m.data_ptr(), v.data_ptr(), shadow.data_ptr()
+            for i in range(world):
+                e.weight[i] = 1.0 / world
+            e.opt = L.make_optim(opt, 1, 1e-2)
+            if variant == "update_cast":
+                L.check(L.lib().ldnn_allreduce_fused(C.byref(c), C.byref(e), None))
+            else:
+                L.check(L.lib().ldnn_allreduce_nvls(C.byref(c), C.byref(e), None, None, None))
+            emu.ok()
+            # emulate mode: every rank's tail writes the one shared shadow from its own (identical) parameters
+            assert torch.equal(shadow, params[0].bfloat16()), (variant, delay_block)
+            outs.append(torch.stack(params).clone())
+    assert torch.equal(outs[0], outs[1]), variant

@@ -25,20 +25,26 @@ ODD = [
 ]
 
 
-def _run(case, mode, **kw):
-    from gpu_util import fp32_mode, make_conv_case, ref_conv, ref_conv_grads, rel_err
+DT = ["bf16", "tf32"]
+
+
+def _run(case, mode, dt="bf16", **kw):
+    """max-rel error of one native conv launch vs the fp32 cuDNN reference (TF32 off).  dt = "tf32": fp32
+    tensors in, tcgen05 kind::tf32 (the reference's precision); "bf16": bf16 tensors, kind::f16."""
+    from gpu_util import DTYPES, fp32_mode, make_conv_case, ref_conv, ref_conv_grads, rel_err
     from ldnn_b200.ops import native_ops as K
     fp32_mode()
     N, H, W, Cin, Cout, R, s, p = case
-    x, w, dy, P, Q = make_conv_case(*case)
+    dtype = DTYPES[dt]
+    x, w, dy, P, Q = make_conv_case(*case, dtype=dtype)
     if mode == K.FPROP:
-        y = torch.full((N, P, Q, Cout), float("nan"), device="cuda", dtype=torch.bfloat16)
+        y = torch.full((N, P, Q, Cout), float("nan"), device="cuda", dtype=dtype)
         K.ConvPlan(K.FPROP, N, H, W, Cin, Cout, R, s, p, x, w.view(Cout, -1), y, **kw).run()
         torch.cuda.synchronize()
         return rel_err(y, ref_conv(x, w, s, p))
     dx_ref, dw_ref = ref_conv_grads(x, w, dy, s, p)
     if mode == K.DGRAD:
-        dx = torch.zeros(N, H, W, Cin, device="cuda", dtype=torch.bfloat16)
+        dx = torch.zeros(N, H, W, Cin, device="cuda", dtype=dtype)
         K.ConvPlan(K.DGRAD, N, H, W, Cin, Cout, R, s, p, dx, w.view(Cout, -1), dy, addend=dx, accumulate=True, **kw).run()
         torch.cuda.synchronize()
         return rel_err(dx, dx_ref)
@@ -49,47 +55,58 @@ def _run(case, mode, **kw):
     return rel_err(dw.view(Cout, R, R, Cin), dw_ref)
 
 
+def _tol(dt):
+    from gpu_util import TOL
+    return TOL[dt]
+
+
+@pytest.mark.parametrize("dt", DT)
 @pytest.mark.parametrize("case", ENHANCED + ODD)
-def test_fprop(case):
+def test_fprop(case, dt):
     from ldnn_b200.ops import native_ops as K
-    assert _run(case, K.FPROP) < 1.5e-2
+    assert _run(case, K.FPROP, dt) < _tol(dt)[0]
 
 
+@pytest.mark.parametrize("dt", DT)
 @pytest.mark.parametrize("case", [c for c in ENHANCED + ODD])
-def test_dgrad(case):
+def test_dgrad(case, dt):
     from ldnn_b200.ops import native_ops as K
-    assert _run(case, K.DGRAD) < 1.5e-2
+    assert _run(case, K.DGRAD, dt) < _tol(dt)[0]
 
 
+@pytest.mark.parametrize("dt", DT)
 @pytest.mark.parametrize("case", ENHANCED + ODD)
-def test_wgrad(case):
+def test_wgrad(case, dt):
     from ldnn_b200.ops import native_ops as K
-    assert _run(case, K.WGRAD) < 5e-3
+    assert _run(case, K.WGRAD, dt) < _tol(dt)[1]
 
 
+@pytest.mark.parametrize("dt", DT)
 @pytest.mark.parametrize("case", ENHANCED[:6] + ODD[:3])
-def test_wgrad_atomic_split_k(case):
+def test_wgrad_atomic_split_k(case, dt):
     """split-K partial tiles red.add'ed into a pre-zeroed dw (the engine's fast path)."""
     from ldnn_b200.ops import native_ops as K
-    assert _run(case, K.WGRAD, atomic_out=True) < 5e-3
+    assert _run(case, K.WGRAD, dt, atomic_out=True) < _tol(dt)[1]
 
 
+@pytest.mark.parametrize("dt", DT)
 @pytest.mark.parametrize("splits", [1, 2, 5])
 @pytest.mark.parametrize("block_n", [64, 128, 256])
-def test_tile_and_split_variants(splits, block_n):
+def test_tile_and_split_variants(splits, block_n, dt):
     from ldnn_b200.ops import native_ops as K
     case = (8, 8, 8, 256, 256, 3, 1, 1)
-    assert _run(case, K.FPROP, splits=splits, block_n=block_n) < 1.5e-2
-    assert _run(case, K.DGRAD, splits=splits, block_n=block_n) < 1.5e-2
-    assert _run(case, K.WGRAD, splits=splits, block_n=block_n) < 5e-3
+    assert _run(case, K.FPROP, dt, splits=splits, block_n=block_n) < _tol(dt)[0]
+    assert _run(case, K.DGRAD, dt, splits=splits, block_n=block_n) < _tol(dt)[0]
+    assert _run(case, K.WGRAD, dt, splits=splits, block_n=block_n) < _tol(dt)[1]
 
 
-def test_split_k_is_deterministic_and_reusable():
-    from gpu_util import make_conv_case
+@pytest.mark.parametrize("dt", DT)
+def test_split_k_is_deterministic_and_reusable(dt):
+    from gpu_util import DTYPES, make_conv_case
     from ldnn_b200.ops import native_ops as K
     N, H, W, Cin, Cout, R, s, p = case = (64, 2, 2, 1024, 1024, 3, 1, 1)
-    x, w, dy, P, Q = make_conv_case(*case)
-    y = torch.empty(N, P, Q, Cout, device="cuda", dtype=torch.bfloat16)
+    x, w, dy, P, Q = make_conv_case(*case, dtype=DTYPES[dt])
+    y = torch.empty(N, P, Q, Cout, device="cuda", dtype=DTYPES[dt])
     plan = K.ConvPlan(K.FPROP, N, H, W, Cin, Cout, R, s, p, x, w.view(Cout, -1), y)
     assert plan.scratch_bytes > 0
     plan.run(); torch.cuda.synchronize(); y0 = y.clone()
@@ -100,18 +117,20 @@ def test_split_k_is_deterministic_and_reusable():
 
 @pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (6, 8, 8, 256, 512, 3, 2, 1), (64, 2, 2, 1024, 1024, 3, 1, 1)])
 @pytest.mark.parametrize("relu", [True, False])
-def test_dgrad_fused_bn_backward_reduce(case, relu):
+@pytest.mark.parametrize("dt", DT)
+def test_dgrad_fused_bn_backward_reduce(case, relu, dt):
     """dgrad epilogue also accumulates (sum dy, sum dy*xhat) of the layer that owns dx."""
-    from gpu_util import make_conv_case
+    from gpu_util import DTYPES, make_conv_case
     from ldnn_b200.ops import native_ops as K
     N, H, W, Cin, Cout, R, s, p = case
-    x, w, dy, P, Q = make_conv_case(*case)
+    dtype = DTYPES[dt]
+    x, w, dy, P, Q = make_conv_case(*case, dtype=dtype)
     g = torch.Generator().manual_seed(11)
-    out = torch.randn(N, H, W, Cin, generator=g).cuda().bfloat16()          # owner's post-activation output
-    y = torch.randn(N, H, W, Cin, generator=g).cuda().bfloat16()            # owner's pre-BN output
+    out = torch.randn(N, H, W, Cin, generator=g).cuda().to(dtype)          # owner's post-activation output
+    y = torch.randn(N, H, W, Cin, generator=g).cuda().to(dtype)            # owner's pre-BN output
     mean, invstd = torch.randn(Cin, generator=g).cuda() * 0.1, (torch.rand(Cin, generator=g) + 0.5).cuda()
     sums = torch.zeros(2 * Cin, device="cuda")
-    dx = torch.zeros(N, H, W, Cin, device="cuda", dtype=torch.bfloat16)
+    dx = torch.zeros(N, H, W, Cin, device="cuda", dtype=dtype)
     K.ConvPlan(K.DGRAD, N, H, W, Cin, Cout, R, s, p, dx, w.view(Cout, -1), dy, addend=dx, accumulate=True,
                bn_bwd_fuse=(out, y, mean, invstd, sums, relu)).run()
     torch.cuda.synchronize()
@@ -127,11 +146,12 @@ def test_dgrad_fused_bn_backward_reduce(case, relu):
 @pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (64, 8, 8, 256, 256, 3, 1, 1),
                                   (64, 16, 16, 128, 256, 3, 2, 1), (8, 14, 14, 256, 256, 3, 1, 1)])
 @pytest.mark.parametrize("splits", [1, 3])
-def test_cluster_multicast_weights(case, splits):
+@pytest.mark.parametrize("dt", DT)
+def test_cluster_multicast_weights(case, splits, dt):
     """Clusters of two M tiles: each CTA loads half of the weight tile and TMA-multicasts it to both."""
     from ldnn_b200.ops import native_ops as K
-    assert _run(case, K.FPROP, cluster=2, block_n=128, splits=splits) < 1.5e-2
-    assert _run(case, K.DGRAD, cluster=2, block_n=128, splits=splits) < 1.5e-2
+    assert _run(case, K.FPROP, dt, cluster=2, block_n=128, splits=splits) < _tol(dt)[0]
+    assert _run(case, K.DGRAD, dt, cluster=2, block_n=128, splits=splits) < _tol(dt)[0]
 
 
 @pytest.mark.skipif(not os.environ.get("LDNN_TEST_PAIR"), reason="staged cta_group::2 variant: not yet run on hardware "
@@ -140,24 +160,26 @@ def test_cluster_multicast_weights(case, splits):
                                   (64, 16, 16, 128, 256, 3, 2, 1), (8, 14, 14, 256, 256, 3, 1, 1)])
 @pytest.mark.parametrize("block_n", [128, 256])
 @pytest.mark.parametrize("splits", [1, 3])
-def test_cta_pair_umma_m256(case, block_n, splits):
+@pytest.mark.parametrize("dt", DT)
+def test_cta_pair_umma_m256(case, block_n, splits, dt):
     """cluster=-2: the two CTAs of a pair run one tcgen05.mma.cta_group::2 (UMMA_M = 256); each loads half of B."""
     from ldnn_b200.ops import native_ops as K
     N, H, W, Cin, Cout, R, s, p = case
     if Cout % block_n == 0:
-        assert _run(case, K.FPROP, cluster=-2, block_n=block_n, splits=splits) < 1.5e-2
+        assert _run(case, K.FPROP, dt, cluster=-2, block_n=block_n, splits=splits) < _tol(dt)[0]
     if Cin % block_n == 0:
-        assert _run(case, K.DGRAD, cluster=-2, block_n=block_n, splits=splits) < 1.5e-2
+        assert _run(case, K.DGRAD, dt, cluster=-2, block_n=block_n, splits=splits) < _tol(dt)[0]
 
 
 @pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (8, 56, 56, 64, 256, 1, 1, 0), (6, 8, 8, 256, 512, 3, 2, 1)])
 @pytest.mark.parametrize("block_n", [64, 128, 256])
-def test_lite_launch_two_ctas_per_sm(case, block_n):
+@pytest.mark.parametrize("dt", DT)
+def test_lite_launch_two_ctas_per_sm(case, block_n, dt):
     """Short-pipeline launch (fewer smem stages, 4 epilogue warps) used for large grids."""
     from ldnn_b200.ops import native_ops as K
     N, H, W, Cin, Cout, R, s, p = case
     if Cout % block_n == 0:
-        assert _run(case, K.FPROP, lite=True, block_n=block_n) < 1.5e-2
+        assert _run(case, K.FPROP, dt, lite=True, block_n=block_n) < _tol(dt)[0]
     if Cin % block_n == 0:
-        assert _run(case, K.DGRAD, lite=True, block_n=block_n) < 1.5e-2
-        assert _run(case, K.WGRAD, lite=True, block_n=block_n, atomic_out=True) < 5e-3
+        assert _run(case, K.DGRAD, dt, lite=True, block_n=block_n) < _tol(dt)[0]
+        assert _run(case, K.WGRAD, dt, lite=True, block_n=block_n, atomic_out=True) < _tol(dt)[1]

@@ -5,6 +5,8 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
+DT = ["tf32", "bf16"]
+
 
 def _engines(spec_fn, batch, kind="adam", lr=1e-3, **kw):
     from gpu_util import fp32_mode
@@ -25,9 +27,10 @@ def _batch(n, seed, hw=32, classes=10):
     return torch.randn(n, 3, hw, hw, generator=g).cuda(), torch.randint(0, classes, (n,), generator=g).cuda()
 
 
-def test_state_dict_roundtrip_reference_layout():
+@pytest.mark.parametrize("dt", DT)
+def test_state_dict_roundtrip_reference_layout(dt):
     from ldnn_b200.models import enhanced_cnn_spec
-    te, ne = _engines(enhanced_cnn_spec, 8)
+    te, ne = _engines(enhanced_cnn_spec, 8, dtype=dt)
     a, b = te.state_dict(), ne.state_dict()
     assert list(a.keys()) == list(b.keys()) and len(b) == 128
     for k in a:
@@ -35,24 +38,34 @@ def test_state_dict_roundtrip_reference_layout():
         assert torch.equal(a[k].cpu(), b[k].cpu()), k
 
 
+# Fixed per-tensor floors for the gradient's cosine against the fp32 torch oracle (TF32 off) on a 64-sample noise
+# batch through the randomly initialised 21-layer net, and for the loss.  tf32 keeps fp32 storage and only rounds
+# the MMA operands to 11 significand bits; bf16 also rounds every stored activation to 8 bits, and the rounding
+# noise is amplified layer by layer on the way down (deepest = first layers): measured worst tensor 0.912-0.923 for the
+# native bf16 engine, 0.924 for torch's own bf16 autocast of the same model (printed by the test) — hence 0.90.
+FLOORS = {"tf32": dict(cos=0.999, ratio=0.02, loss=2e-3), "bf16": dict(cos=0.90, ratio=0.15, loss=3e-2)}
+
+
+@pytest.mark.parametrize("dt", DT)
 @pytest.mark.parametrize("use_graph,deterministic", [(False, False), (True, False), (True, True)])
-def test_forward_backward_matches_torch(use_graph, deterministic, monkeypatch):
+def test_forward_backward_matches_torch(use_graph, deterministic, dt, monkeypatch):
     from ldnn_b200.models import enhanced_cnn_spec
     if deterministic:
         monkeypatch.setenv("LDNN_DETERMINISTIC", "1")
     else:
         monkeypatch.delenv("LDNN_DETERMINISTIC", raising=False)
-    te, ne = _engines(enhanced_cnn_spec, 64, use_graph=use_graph)
+    te, ne = _engines(enhanced_cnn_spec, 64, use_graph=use_graph, dtype=dt)
+    fl = FLOORS[dt]
     x, y = _batch(64, 1)
     for it in range(3):       # eager warm-up, capture, replay
         lt, ct = te.train_step(x, y, update=False)
         ln, cn = ne.train_step(x, y, update=False)
-        assert abs(float(lt) - float(ln)) < 3e-2 * max(1.0, abs(float(lt))), (it, float(lt), float(ln))
-    # Gradient parity per tensor.  fp32 is the oracle, but a 21-layer randomly initialised net on noise
-    # amplifies rounding differences layer by layer, so the yardstick for "bf16-correct" is torch's own
-    # bf16 autocast run of the same model: we must agree with fp32 about as well as autocast does.
+        assert abs(float(lt) - float(ln)) < fl["loss"] * max(1.0, abs(float(lt))), (it, float(lt), float(ln))
+    # Gradient parity per tensor against the fp32 oracle, with fixed floors.  torch's own bf16 autocast run of the
+    # same model is printed beside it as a yardstick (how well ANY bf16 execution agrees with fp32 here).
     amp = _autocast_grads(te, x, y)
     worst = 1.0
+    report = []
     for s in te.flat.slots:
         gt = te.flat.view(te.flat.grads, s.key).float()
         gn = ne.export_tensor(ne.flat.grads, s.key).cuda().float()
@@ -62,8 +75,11 @@ def test_forward_backward_matches_torch(use_graph, deterministic, monkeypatch):
         cos_amp = float((gt * amp[s.key]).sum() / (gt.norm() * amp[s.key].norm() + 1e-20))
         ratio = float(gn.norm() / gt.norm())
         worst = min(worst, cos)
-        assert cos > min(0.98, cos_amp - 0.03) and 0.85 < ratio < 1.15, (s.key, cos, cos_amp, ratio)
-    assert worst > 0.85
+        report.append((s.key, round(cos, 5), round(cos_amp, 5), round(ratio, 4)))
+    print(f"[grad parity {dt} graph={use_graph} det={deterministic}] worst cos {worst:.5f}; "
+          f"lowest 5: {sorted(report, key=lambda r: r[1])[:5]}")
+    for key, cos, cos_amp, ratio in report:
+        assert cos > fl["cos"] and abs(ratio - 1.0) < fl["ratio"], (key, cos, cos_amp, ratio)
 
 
 def _autocast_grads(te, x, y):
@@ -79,9 +95,10 @@ def _autocast_grads(te, x, y):
     return {k: p.grad.detach().float() for k, p in m.named_parameters()}
 
 
-def test_training_curve_tracks_torch():
+@pytest.mark.parametrize("dt", DT)
+def test_training_curve_tracks_torch(dt):
     from ldnn_b200.models import enhanced_cnn_spec
-    te, ne = _engines(enhanced_cnn_spec, 64)
+    te, ne = _engines(enhanced_cnn_spec, 64, dtype=dt)
     lt, ln = [], []
     for it in range(12):
         x, y = _batch(64, 100 + it % 3)         # 3 recurring batches → loss must fall
@@ -89,7 +106,7 @@ def test_training_curve_tracks_torch():
         b, _ = ne.train_step(x, y)
         lt.append(float(a)); ln.append(float(b))
     assert ln[-1] < ln[0] * 0.7, ln
-    assert abs(ln[-1] - lt[-1]) < 0.35 * max(lt[0], 1.0), (lt, ln)
+    assert abs(ln[-1] - lt[-1]) < (0.35 if dt == "bf16" else 0.1) * max(lt[0], 1.0), (lt, ln)
     # eval path + BN running stats
     x, y = _batch(64, 100)
     l1, c1, p1 = te.eval_step(x, y)
@@ -100,10 +117,11 @@ def test_training_curve_tracks_torch():
     assert torch.allclose(sd["prep.1.running_mean"].cpu(), te.state_dict()["prep.1.running_mean"].cpu(), atol=5e-2)
 
 
-def test_partial_batch_and_checkpoint(tmp_path):
+@pytest.mark.parametrize("dt", DT)
+def test_partial_batch_and_checkpoint(tmp_path, dt):
     from ldnn_b200.models import enhanced_cnn_spec
     from ldnn_b200.utils.checkpoint import load_checkpoint, save_checkpoint
-    te, ne = _engines(enhanced_cnn_spec, 64)
+    te, ne = _engines(enhanced_cnn_spec, 64, dtype=dt)
     x, y = _batch(6, 7)
     a, _ = te.train_step(x, y)
     b, _ = ne.train_step(x, y)
@@ -116,23 +134,24 @@ def test_partial_batch_and_checkpoint(tmp_path):
     assert load_checkpoint(path, te) == 3
     for k in ("layer4.1.conv2.weight", "prep.0.weight", "fc.bias"):
         assert torch.allclose(te.export_tensor(te.flat.m, k), ne.export_tensor(ne.flat.m, k), atol=1e-7), k
-    ne2 = _engines(enhanced_cnn_spec, 64)[1]
+    ne2 = _engines(enhanced_cnn_spec, 64, dtype=dt)[1]
     load_checkpoint(path, ne2)
     assert torch.equal(ne2.flat.params, ne.flat.params) and ne2.flat.step == ne.flat.step
 
 
-def test_resnet50_small_image_step():
+@pytest.mark.parametrize("dt", DT)
+def test_resnet50_small_image_step(dt):
     """ResNet-50 graph (bottlenecks, 7x7 stem via im2col, max-pool) at 64x64 to keep it quick."""
     from ldnn_b200.models import resnet50_spec
     spec_fn = lambda: resnet50_spec(num_classes=100, in_hw=64)
-    te, ne = _engines(spec_fn, 8, kind="sgd", lr=1e-2)
+    te, ne = _engines(spec_fn, 8, kind="sgd", lr=1e-2, dtype=dt)
     x, y = _batch(8, 3, hw=64, classes=100)
     for _ in range(2):
         a, _ = te.train_step(x, y, update=False)
         b, _ = ne.train_step(x, y, update=False)
     # 53 random-init layers at batch 8 amplify bf16 rounding; the loss agrees to ~10 % and the
     # gradient nearest the output (fc) must line up with fp32
-    assert abs(float(a) - float(b)) < 0.1 * max(1.0, float(a)), (float(a), float(b))
+    assert abs(float(a) - float(b)) < (0.1 if dt == "bf16" else 0.01) * max(1.0, float(a)), (float(a), float(b))
     gt = te.flat.view(te.flat.grads, "fc.weight").float()
     gn = ne.export_tensor(ne.flat.grads, "fc.weight").cuda().float()
-    assert float((gt * gn).sum() / (gt.norm() * gn.norm())) > 0.9
+    assert float((gt * gn).sum() / (gt.norm() * gn.norm())) > (0.9 if dt == "bf16" else 0.995)
