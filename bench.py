@@ -420,8 +420,15 @@ def run_reference(a):
             y = torch.randint(0, 10, (k * a.batch,), generator=g)
             return DataLoader(TensorDataset(x, y), batch_size=a.batch, shuffle=False)
 
+        import inspect
+        # four of the six directories take two extra (unused) arguments: (..., device, world_size, scheduler, epoch)
+        long_sig = "world_size" in inspect.signature(train_local_epoch).parameters
+
         def epoch(ld):
-            train_local_epoch(model, ld, criterion, optimizer, device, scheduler)
+            if long_sig:
+                train_local_epoch(model, ld, criterion, optimizer, device, world, scheduler, 0)
+            else:
+                train_local_epoch(model, ld, criterion, optimizer, device, scheduler)
             if topology == "allreduce":
                 if a.aggregation_type == "weighted" and world > 1:
                     average_gradients_weighted(model, world, 0.5)

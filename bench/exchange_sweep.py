@@ -1,8 +1,19 @@
 #!/usr/bin/env python
 """Gradient-exchange bandwidth sweep 1 KB – 1 GB (BASELINE config 5): fused P2P all-reduce / ring /
-double-ring vs NCCL all_reduce on the same buffers.  Launch with torchrun (one process per GPU).
+double-ring (and the in-switch NVLS all-reduce when LDNN_NVLS=1 gives a multicast mapping) vs NCCL all_reduce on
+the same buffers.  Launch with torchrun (one process per GPU).
+
+Two modes per size:
+  reduce  the bare exchange: ours = one kernel (reduce + 1/W scale); NCCL arm = dist.all_reduce + the reference's
+          separate scale kernel (Balanced All-Reduce/communication.py:24-25)
+  update  the fused product form: ours = ONE kernel (reduce + scale + Adam on the owned slice + push of the updated
+          parameters); NCCL arm = all_reduce + scale + torch's fused Adam over the whole slab.
+
 Device-timed (CUDA events), max over ranks; algorithmic bytes = payload size; bus bandwidth =
-2*(ws-1)/ws * bytes / time (the all-reduce convention)."""
+2*(ws-1)/ws * bytes / time (the all-reduce convention); `link_frac` = busbw / 770 GB/s (the measured peer-copy
+rate per direction per GPU, B200_PROFILING.md) = achieved fraction of the NVLink roofline; for `update` the roofline
+is the slower of that link time and the HBM time of the tail.  SM clocks and throttle reasons are sampled during
+the whole sweep and written into the same output files as the table."""
 import argparse
 import ctypes as C
 import json
@@ -15,25 +26,36 @@ import torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
+LINK_GBS = 770.0     # measured peer copy, per direction per GPU
+HBM_GBS = 6554.6     # MEASURED_PEAKS.json
+
 
 class _Flat:
     pass
 
 
 class _Eng:
-    """Minimal engine facade: flat fp32 slabs in symmetric memory."""
+    """Minimal engine facade: flat fp32 slabs in symmetric memory (multicast-capable when LDNN_NVLS=1)."""
 
-    def __init__(self, n, dev):
+    def __init__(self, n, dev, with_moments):
         from ldnn_b200.ops import native_ops as K
         self._symm, self.flat, self.shadow = {}, _Flat(), None
         for name in ("params", "grads"):
-            t, h, p = K.symm_alloc(n * 4, dev)
+            if K.nvls_requested():
+                t, h, p = K.symm_alloc_multicast(n * 4, dev)
+            else:
+                t, h, p = K.symm_alloc(n * 4, dev)
             self._symm[name] = (t, h, p)
             setattr(self.flat, name, t.view(torch.float32))
-        self.flat.total, self.flat.m, self.flat.v = n, None, None
+        self.flat.total = n
+        self.flat.m = torch.zeros(n, device=dev) if with_moments else None
+        self.flat.v = torch.zeros(n, device=dev) if with_moments else None
 
     def symm_handle(self, name):
         return self._symm[name][1], self._symm[name][2], self.flat.total * 4
+
+    def symm_tensor(self, name):
+        return self._symm[name][0]
 
     def params_changed(self):
         pass
@@ -44,61 +66,96 @@ def main():
     ap.add_argument("--max_mb", type=int, default=1024)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--blocks", type=int, default=64)   # the sweep has the GPU to itself: 64 CTAs for every kernel
+    ap.add_argument("--modes", default="reduce,update")
     ap.add_argument("--out", default="gpurun_out/exchange_sweep.json")
     a = ap.parse_args()
+    from ldnn_b200.engine import OptimConfig
     from ldnn_b200.launch import init_runtime, shutdown
+    from ldnn_b200.ops import _lib as L
     from ldnn_b200.parallel.exchange import ExchangeSpec
     from ldnn_b200.parallel.fused import FusedExchanger
-    from ldnn_b200.utils.timing import max_over_ranks
+    from ldnn_b200.utils.timing import ClockSampler, max_over_ranks
     rt = init_runtime("nccl", seed=0)
     ws, dev = rt.world_size, rt.device
     nmax = a.max_mb * (1 << 20) // 4
-    eng = _Eng(nmax, dev)
+    modes = [m for m in a.modes.split(",") if m]
+    eng = _Eng(nmax, dev, "update" in modes)
     eng.flat.grads.normal_()
+    eng.flat.params.normal_()
+    opt = OptimConfig(kind="adam", lr=1e-3)
     rows = []
     sizes = [1 << k for k in range(10, 31) if (1 << k) <= a.max_mb << 20]
-    for topo in ["allreduce", "ring", "double_ring", "nccl"]:
-        ex = None
-        if topo != "nccl":
-            ex = FusedExchanger(ExchangeSpec(topo, "allreduce", "equal", 0.5, None, ws), rt, eng, comm_blocks=a.blocks)
-        for nbytes in sizes:
-            n = max(nbytes // 4, 4 * ws)
-            if ex is not None:
-                ex.n = n
-            buf = eng.flat.grads[:n]
+    impls = ["allreduce", "ring", "double_ring", "nccl"]
+    clk = ClockSampler(dev.index or 0, period_s=0.1)
+    clk.__enter__()
+    nvls_seen = False
+    for mode in modes:
+        for topo in impls:
+            ex = None
+            if topo != "nccl":
+                ex = FusedExchanger(ExchangeSpec(topo, "allreduce", "equal", 0.5, None, ws), rt, eng, comm_blocks=a.blocks)
+                nvls_seen = nvls_seen or bool(getattr(ex, "nvls", False))
+            for nbytes in sizes:
+                n = max(nbytes // 4, 4 * ws)
+                if ex is not None:
+                    ex.n = n
+                buf = eng.flat.grads[:n]
+                step = [0]
+                topt = None
+                if mode == "update" and ex is None:
+                    pp = torch.nn.Parameter(eng.flat.params[:n])
+                    pp.grad = buf
+                    topt = torch.optim.Adam([pp], lr=opt.lr, fused=True)     # torch's fused (multi-tensor) Adam
 
-            def one():
-                if ex is None:
-                    dist.all_reduce(buf)
-                    buf.mul_(1.0 / ws)            # the reference's separate scale kernel
-                else:
-                    ex._launch_reduce(ex._exchange_struct("grads", 0))
-            iters = a.iters if nbytes <= (64 << 20) else max(3, a.iters // 4)
-            for _ in range(3):
-                one()
-            dist.barrier(); torch.cuda.synchronize()
-            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            t0.record()
-            for _ in range(iters):
-                one()
-            t1.record(); torch.cuda.synchronize()
-            ms = max_over_ranks(t0.elapsed_time(t1) / iters, dev)
-            rows.append({"impl": topo, "bytes": n * 4, "us": ms * 1e3, "algbw_GBs": n * 4 / ms / 1e6,
-                         "busbw_GBs": 2 * (ws - 1) / ws * n * 4 / ms / 1e6, "world": ws})
-            buf.normal_()
-        if ex is not None:
-            ex.check(); ex.close()
+                def one():
+                    step[0] += 1
+                    if ex is None:
+                        dist.all_reduce(buf)
+                        buf.mul_(1.0 / ws)            # the reference's separate scale kernel
+                        if topt is not None:
+                            topt.step()
+                    elif mode == "update":
+                        ex._launch_reduce(ex._exchange_struct("grads", L.X_UPDATE, L.make_optim(opt, step[0], opt.lr)))
+                    else:
+                        ex._launch_reduce(ex._exchange_struct("grads", 0))
+                iters = a.iters if nbytes <= (64 << 20) else max(3, a.iters // 4)
+                for _ in range(3):
+                    one()
+                dist.barrier(); torch.cuda.synchronize()
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record()
+                for _ in range(iters):
+                    one()
+                t1.record(); torch.cuda.synchronize()
+                ms = max_over_ranks(t0.elapsed_time(t1) / iters, dev)
+                nb = n * 4
+                bus = 2 * (ws - 1) / ws * nb / ms / 1e6
+                t_link = 2 * (ws - 1) / ws * nb / (LINK_GBS * 1e9)
+                t_hbm = ((3 + 7 / ws) * nb / (HBM_GBS * 1e9)) if mode == "update" else (3 * nb / (HBM_GBS * 1e9))
+                rows.append({"mode": mode, "impl": topo, "bytes": nb, "us": ms * 1e3, "algbw_GBs": nb / ms / 1e6,
+                             "busbw_GBs": bus, "link_frac": bus / LINK_GBS if ws > 1 else None,
+                             "roofline_frac": max(t_link, t_hbm) / (ms / 1e3), "world": ws,
+                             "nvls": bool(ex is not None and getattr(ex, "nvls", False) and topo == "allreduce")})
+                buf.normal_()
+            if ex is not None:
+                ex.check(); ex.close()
+    clk.__exit__(None, None, None)
+    clocks = clk.summary()
     if rt.rank == 0:
         os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
         with open(a.out, "w") as f:
-            json.dump(rows, f, indent=1)
-        print(f"{'bytes':>12} " + " ".join(f"{t:>14}" for t in ["allreduce", "ring", "double_ring", "nccl"]) + "   (busbw GB/s | us)")
-        for nb in sorted({r["bytes"] for r in rows}):
-            cells = []
-            for t in ["allreduce", "ring", "double_ring", "nccl"]:
-                r = [x for x in rows if x["impl"] == t and x["bytes"] == nb][0]
-                cells.append(f"{r['busbw_GBs']:7.1f}|{r['us']:6.0f}")
-            print(f"{nb:>12} " + " ".join(f"{c:>14}" for c in cells))
+            json.dump({"world": ws, "clocks": clocks, "nvls": nvls_seen, "link_GBs": LINK_GBS, "rows": rows}, f, indent=1)
+        print(f"# exchange sweep, {ws} x B200, blocks={a.blocks}, NVLS all-reduce: {nvls_seen}")
+        print(f"# clocks during the sweep: {json.dumps(clocks)}")
+        for mode in modes:
+            print(f"## mode = {mode}   cells: busbw GB/s | us | fraction of roofline")
+            print(f"{'bytes':>12} " + " ".join(f"{t:>22}" for t in impls))
+            for nb in sorted({r["bytes"] for r in rows}):
+                cells = []
+                for t in impls:
+                    r = [x for x in rows if x["impl"] == t and x["bytes"] == nb and x["mode"] == mode][0]
+                    cells.append(f"{r['busbw_GBs']:7.1f}|{r['us']:6.0f}|{r['roofline_frac']:5.2f}")
+                print(f"{nb:>12} " + " ".join(f"{c:>22}" for c in cells))
     shutdown(rt)
 
 

@@ -293,6 +293,19 @@ allreduce_nvls_kernel(const ldnn_comm c, const ldnn_exchange e, float4* const mc
 //   W <= k <= 2W-3 : wait(k-1); forward the finished chunk c = c0-k+W from own slab -> next slab
 //   end            : wait(2W-3) (last chunk has landed), bf16 cast of what arrived
 // Flags: sig[kBarWords + ((ring*J + j) * 16 + k)] in the CONSUMER's pad, value = this call's sequence.
+//
+// A CTA is four independent GROUPS of 128 threads (named barriers 1..4).  Every hop of a sub-chunk ends in
+// "all stores issued -> system-scope release -> flag", during which its issuer sends nothing; with four
+// chains per SM (and many short sub-chunks instead of a few long ones) another group is always streaming
+// while one drains.  With two rings, groups 0,2 of EVERY CTA drive ring 0 and groups 1,3 ring 1: each ring
+// gets all SMs of the launch (the two directions use different link directions and only share issue slots).
+constexpr int kGroups = 4;
+constexpr int kGroupThreads = kCommThreads / kGroups;
+
+__device__ __forceinline__ void group_sync(int grp) {
+  asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "n"(kGroupThreads) : "memory");
+}
+
 __global__ void __launch_bounds__(kCommThreads, 1)
 ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings, const int J, const long long sub4) {
   const Ctx x = make_ctx(c);
@@ -304,9 +317,10 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
 
   comm_barrier(x, seq + 1);     // every rank's slab is final and last call's staging is drained
 
-  const int blocks_per_ring = x.blocks / num_rings;
-  const int ring = min(x.block / blocks_per_ring, num_rings - 1);
-  const int bir = x.block - ring * blocks_per_ring;
+  const int grp = threadIdx.x / kGroupThreads, gt = threadIdx.x % kGroupThreads;
+  const int ring = (num_rings == 2) ? (grp & 1) : 0;
+  const int groups_per_ring = x.blocks * kGroups / num_rings;                       // chains of this ring, per rank
+  const int gir = (num_rings == 2) ? (x.block * (kGroups / 2) + (grp >> 1)) : (x.block * kGroups + grp);
   const int dir = (ring == 0) ? 1 : -1;
   const int next = ((r + dir) % W + W) % W;
   const long long reg_lo = n4 * ring / num_rings, reg_hi = n4 * (ring + 1) / num_rings;
@@ -332,19 +346,19 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
     int cidx = (k <= W - 1) ? (r - dir * k) : (r - dir * (k - W));
     cidx = ((cidx % W) + W) % W;
     const long long c_lo = min(reg_lo + (long long)cidx * chunk4, reg_hi), c_hi = min(c_lo + chunk4, reg_hi);
-    for (int j = bir; j < J; j += blocks_per_ring) {
+    for (int j = gir; j < J; j += groups_per_ring) {
       const long long lo = min(c_lo + (long long)j * sub4, c_hi), hi = min(lo + sub4, c_hi);
       const int fidx = (ring * J + j) * 16;
       if (k > 0) {
-        if (threadIdx.x == 0 && alive) alive = spin_until(x, my_flags + fidx + (k - 1), seq + 2);
-        __syncthreads();
+        if (gt == 0 && alive) alive = spin_until(x, my_flags + fidx + (k - 1), seq + 2);
+        group_sync(grp);
       }
       constexpr int U = 4;
-      for (long long base = lo + threadIdx.x; base < hi; base += (long long)U * kCommThreads) {
+      for (long long base = lo + gt; base < hi; base += (long long)U * kGroupThreads) {
         float4 a[U], g[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const long long i = base + (long long)u * kCommThreads;
+          const long long i = base + (long long)u * kGroupThreads;
           if (i >= hi) continue;
           if (k >= W) a[u] = my_final[i];                  // finished chunk that prev stored here
           else {
@@ -354,7 +368,7 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const long long i = base + (long long)u * kCommThreads;
+          const long long i = base + (long long)u * kGroupThreads;
           if (i >= hi) continue;
           if (k < W - 1) {                                  // reduce-scatter hop
             const float4 acc = (k == 0) ? f4_scale(g[u], wr) : f4_fma(g[u], wr, a[u]);
@@ -377,11 +391,10 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
         }
       }
       if (k < nmsg) {
-        __syncthreads();
-        if (threadIdx.x == 0) {
-          __threadfence_system();
-          st_release_sys(next_flags + fidx + k, seq + 2);
-        }
+        // the group's stores happen-before thread 0's release through the barrier; st.release.sys then orders
+        // them (cumulatively) before the flag for the acquiring consumer
+        group_sync(grp);
+        if (gt == 0) st_release_sys(next_flags + fidx + k, seq + 2);
       }
     }
   }
@@ -399,6 +412,147 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
     }
   }
   comm_barrier(x, seq + 3);   // nobody is still storing into a slab that is about to be reused
+}
+
+// ================================================================== K-RING / K-DRING, small and medium payloads
+// The bulk kernel above pays, per hop, a system-scope release plus a flag round trip (~6 us): 2(W-1) dependent hops
+// put its floor near 90 us at 8 GPUs.  Below a few tens of MB the rings therefore run FLAG-FREE: the payload itself
+// says when it has arrived.  Every rank owns a staging pad of three phases; a phase is pre-filled with a sentinel
+// (-0.0f, a bit pattern the sender never emits: it canonicalises -0 to +0, which sums identically).  A hop is
+// one 16-byte store into the next rank's pad; the consumer polls the slot until none of its four words is the
+// sentinel (each 32-bit word is single-copy atomic, so no ordering between words, no fence and no flag is needed),
+// combines and stores onward.  Threads own element indices, so every element runs its own dependency chain around
+// the ring with no CTA-wide synchronisation at all, and there is no kernel-wide barrier: finished chunks travel
+// through the pad too (a peer never writes into another rank's gradient/parameter slab, which may still be in use).
+// Phases: call t (e.ll_epoch, counted over calls of THIS kernel) uses phase t%3 and re-fills phase (t+2)%3 — the
+// one call t-1 used — with the sentinel for call t+2.  A rank cannot finish call t+1 before every peer has started
+// it (its last arrivals depend on all ranks' sends of that call), so nobody writes call t+2 data into a phase that
+// is still being re-filled.  Same message schedule, chunk ownership, weights and fused tail as the bulk kernel.
+__device__ __forceinline__ bool is_sentinel(float f) { return __float_as_uint(f) == 0x80000000u; }
+__device__ __forceinline__ float4 no_sentinel(float4 v) {
+  if (is_sentinel(v.x)) v.x = 0.f;
+  if (is_sentinel(v.y)) v.y = 0.f;
+  if (is_sentinel(v.z)) v.z = 0.f;
+  if (is_sentinel(v.w)) v.w = 0.f;
+  return v;
+}
+__device__ __forceinline__ bool poll_slot(const Ctx& x, const float4* p, float4& v) {
+  v = ld_sys_f4(p);
+  if (!(is_sentinel(v.x) | is_sentinel(v.y) | is_sentinel(v.z) | is_sentinel(v.w))) return true;
+  const long long t0 = clock64();
+  for (;;) {
+    v = ld_sys_f4(p);
+    if (!(is_sentinel(v.x) | is_sentinel(v.y) | is_sentinel(v.z) | is_sentinel(v.w))) return true;
+    if ((unsigned long long)(clock64() - t0) > x.timeout) {
+      if (x.err) atomicExch(x.err, 1);
+      return false;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kCommThreads, 1)
+ring_ll_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings) {
+  const Ctx x = make_ctx(c);
+  const int W = x.world, r = x.rank;
+  const long long n4 = e.n >> 2;
+  const bool update = (e.mode & LDNN_X_UPDATE) != 0;
+  const bool cast = e.shadow != nullptr && (update || (e.mode & 4));
+  const unsigned int phase = e.ll_epoch % 3u, cphase = (e.ll_epoch + 2u) % 3u;
+  const float4 kSent = make_float4(__uint_as_float(0x80000000u), __uint_as_float(0x80000000u),
+                                   __uint_as_float(0x80000000u), __uint_as_float(0x80000000u));
+  // re-arm the phase the previous call used (local stores; nobody touches it before call t+2)
+  {
+    float4* cl = reinterpret_cast<float4*>(e.ll[r]) + (long long)cphase * e.ll_phase4;
+    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < e.ll_clear4;
+         i += (long long)x.blocks * kCommThreads)
+      cl[i] = kSent;
+  }
+  // threads of a CTA split between the rings, so every CTA drives both directions
+  const int tpr = kCommThreads / num_rings;                        // threads per ring in this CTA
+  const int ring = threadIdx.x / tpr, t = threadIdx.x % tpr;
+  const int dir = (ring == 0) ? 1 : -1;
+  const int next = ((r + dir) % W + W) % W;
+  const long long reg_lo = n4 * ring / num_rings, reg_hi = n4 * (ring + 1) / num_rings;
+  const long long chunk4 = (reg_hi - reg_lo + W - 1) / W;
+  const long long slot4 = ((n4 + num_rings - 1) / num_rings + W - 1) / W;       // slot stride: the larger ring's chunk
+  const int nmsg = 2 * (W - 1);
+
+  float4* const gr = reinterpret_cast<float4*>(e.grads[r]);
+  float4* const pr = reinterpret_cast<float4*>(e.params[r]);
+  float4* const my_final = update ? pr : gr;
+  float4* const my_m = reinterpret_cast<float4*>(e.m);
+  float4* const my_v = reinterpret_cast<float4*>(e.v);
+  __nv_bfloat16* const sh = reinterpret_cast<__nv_bfloat16*>(e.shadow);
+  const float4* const my_pad = reinterpret_cast<const float4*>(e.ll[r]) + (long long)phase * e.ll_phase4 +
+                               (long long)ring * nmsg * slot4;
+  float4* const next_pad = reinterpret_cast<float4*>(e.ll[next]) + (long long)phase * e.ll_phase4 +
+                           (long long)ring * nmsg * slot4;
+  const float wr = e.weight[r];
+  bool alive = true;
+
+  for (int k = 0; k <= nmsg && W > 1; ++k) {
+    int cidx = (k <= W - 1) ? (r - dir * k) : (r - dir * (k - W));
+    cidx = ((cidx % W) + W) % W;
+    const long long c_lo = min(reg_lo + (long long)cidx * chunk4, reg_hi), c_hi = min(c_lo + chunk4, reg_hi);
+    const long long len = c_hi - c_lo;
+    constexpr int U = 4;                       // elements per thread in flight: polls and stores of a batch overlap
+    for (long long base = (long long)x.block * tpr + t; base < len; base += (long long)U * x.blocks * tpr) {
+      float4 a[U], g[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long l = base + (long long)u * x.blocks * tpr;
+        if (l >= len) continue;
+        if (k < W) g[u] = gr[c_lo + l];
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long l = base + (long long)u * x.blocks * tpr;
+        if (l >= len) continue;
+        if (k > 0) {
+          if (alive) alive = poll_slot(x, my_pad + (long long)(k - 1) * slot4 + l, a[u]);
+          if (!alive) a[u] = make_float4(0, 0, 0, 0);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long l = base + (long long)u * x.blocks * tpr;
+        if (l >= len) continue;
+        const long long i = c_lo + l;
+        float4 out;
+        if (k < W - 1) {                                    // reduce-scatter hop
+          out = (k == 0) ? f4_scale(g[u], wr) : f4_fma(g[u], wr, a[u]);
+        } else if (k == W - 1) {                            // owner: finish + fused tail
+          out = f4_fma(g[u], wr, a[u]);
+          if (update) {
+            float4 p0 = pr[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
+            optim_update4(p0, out, m0, v0, e.opt);
+            my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
+            out = p0;
+          }
+          out = no_sentinel(out);
+          my_final[i] = out;
+          if (cast) store_bf16x4(sh + 4 * i, out);
+        } else {                                            // all-gather hop: keep and forward what arrived
+          out = a[u];
+          my_final[i] = out;
+          if (cast) store_bf16x4(sh + 4 * i, out);
+        }
+        if (k < nmsg) st_sys_f4(next_pad + (long long)k * slot4 + l, no_sentinel(out));
+      }
+    }
+  }
+  if (W == 1 && (update || cast)) {
+    for (long long i = (long long)x.block * kCommThreads + threadIdx.x; i < n4; i += (long long)x.blocks * kCommThreads) {
+      float4 val = f4_scale(gr[i], e.weight[0]);
+      if (update) {
+        float4 p0 = pr[i], m0 = my_m[i], v0 = e.opt.kind == 0 ? my_v[i] : make_float4(0, 0, 0, 0);
+        optim_update4(p0, val, m0, v0, e.opt);
+        pr[i] = p0; my_m[i] = m0; if (e.opt.kind == 0) my_v[i] = v0;
+        val = p0;
+      }
+      if (cast) store_bf16x4(sh + 4 * i, val);
+    }
+  }
 }
 
 // ================================================================== compat gossip (1- or 2-hop pull)
@@ -550,15 +704,40 @@ extern "C" int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int n
   LDNN_ARG(c->world == 1 || x->recv[c->emulate ? 0 : c->rank] != nullptr, "ring: needs the symmetric `recv` staging slab");
   const long long n4 = x->n / 4;
   const long long chunk4 = (n4 / num_rings + c->world) / c->world + 1;
-  // sub-chunks: every hand-off costs a system fence + a flag round trip, so large payloads use
-  // ~2 sub-chunks per CTA per step (>= 128 KB each); the flag table caps J
-  const int bpr = std::max(1, c->blocks / num_rings);
-  long long sub4 = std::max<long long>(8192, (chunk4 + 2 * bpr - 1) / (2 * bpr));
+  // sub-chunks: one per hand-off chain.  Every group of 128 threads runs its own chain (4 per CTA), so a payload is cut
+  // into ~2 sub-chunks per group per step, never shorter than 16 KB (a hand-off costs a system-scope release + a flag
+  // round trip); the flag table caps J
+  const int gpr = std::max(1, c->blocks * kGroups / num_rings);
+  long long sub4 = std::max<long long>(1024, (chunk4 + 2 * gpr - 1) / (2 * gpr));
   int J = (int)((chunk4 + sub4 - 1) / sub4);
   const int maxJ = kFlagWords / (16 * 2);
   if (J > maxJ) { J = maxJ; sub4 = (chunk4 + J - 1) / J; }
   if (J < 1) J = 1;
   return launch_comm(ring_fused_kernel, *c, (cudaStream_t)stream, *c, *x, num_rings, J, sub4);
+}
+
+extern "C" long long ldnn_ring_ll_slots(long long n, int world, int num_rings) {
+  const long long n4 = n / 4;
+  const long long slot4 = ((n4 + num_rings - 1) / num_rings + world - 1) / world;
+  return (long long)num_rings * 2 * (world - 1) * slot4;
+}
+
+extern "C" int ldnn_ring_ll(const ldnn_comm* c, const ldnn_exchange* x, int num_rings, void* stream) {
+  LDNN_ARG(x->n % 4 == 0, "ring_ll: n %% 4");
+  LDNN_ARG(num_rings == 1 || num_rings == 2, "ring_ll: num_rings=%d", num_rings);
+  LDNN_ARG(!(x->mode & LDNN_X_SELFMIX), "ring_ll: self-weighted mixing is only available on the all-reduce schedule");
+  LDNN_ARG(!(x->mode & LDNN_X_UPDATE) || (x->m && (x->opt.kind == 1 || x->v)), "ring_ll: UPDATE needs m (and v)");
+  LDNN_ARG(c->world == 1 || x->ll[c->emulate ? 0 : c->rank] != nullptr, "ring_ll: needs the symmetric staging pad `ll`");
+  const long long used = ldnn_ring_ll_slots(x->n, c->world, num_rings);
+  LDNN_ARG(used <= x->ll_phase4 && x->ll_clear4 <= x->ll_phase4,
+           "ring_ll: payload needs %lld staging slots per phase, the pad holds %lld", used, x->ll_phase4);
+  // few elements -> few CTAs (every element's chain is independent; idle CTAs would only add launch cost)
+  ldnn_comm cc = *c;
+  const long long slot4 = used / std::max(1, num_rings * 2 * (c->world - 1));
+  const long long clear_ctas = (x->ll_clear4 + kCommThreads * 8 - 1) / (kCommThreads * 8);
+  const long long want = std::max<long long>((slot4 * num_rings + kCommThreads - 1) / kCommThreads, clear_ctas);
+  cc.blocks = (int)std::max<long long>(1, std::min<long long>(c->blocks, want));
+  return launch_comm(ring_ll_kernel, cc, (cudaStream_t)stream, cc, *x, num_rings);
 }
 
 extern "C" int ldnn_gossip_pull(const ldnn_comm* c, void* const* bufs, void* const* recv, long long n, float c_self,

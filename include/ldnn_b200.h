@@ -236,6 +236,12 @@ typedef struct {
   float self_coef;               /* a */
   int mode;
   ldnn_optim opt;
+  /* flag-free small/medium-payload rings (ldnn_ring_ll): per-rank symmetric staging pad of 3 phases x ll_phase4
+   * float4 slots, every word initialised to the sentinel 0x80000000 (-0.0f) by the allocator */
+  void* ll[LDNN_MAX_RANKS];
+  long long ll_phase4;           /* slots per phase */
+  long long ll_clear4;           /* slots the PREVIOUS ldnn_ring_ll call used (re-armed by this call) */
+  unsigned int ll_epoch;         /* number of earlier ldnn_ring_ll calls on this pad (same on every rank) */
 } ldnn_exchange;
 
 /* K-AR: two-shot all-reduce (pull-reduce owned slice, fused tail, push to peers) */
@@ -248,6 +254,12 @@ int ldnn_allreduce_fused(const ldnn_comm* c, const ldnn_exchange* x, void* strea
 int ldnn_allreduce_nvls(const ldnn_comm* c, const ldnn_exchange* x, void* mc_data, void* mc_params, void* stream);
 /* K-RING / K-DRING: reduce-scatter + all-gather around 1 or 2 (counter-rotating) rings */
 int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int num_rings, void* stream);
+/* K-RING / K-DRING for small and medium payloads: the same reduce-scatter + all-gather schedule with no flags, no
+ * fences and no kernel-wide barrier — the payload travels through x->ll and announces itself (sentinel polling), one
+ * dependency chain per element.  ldnn_ring_ll_slots = float4 slots one call uses per phase (pass it as the next call's
+ * ll_clear4).  Hop cost ~ one NVLink store latency instead of store + release + flag. */
+long long ldnn_ring_ll_slots(long long n, int world, int num_rings);
+int ldnn_ring_ll(const ldnn_comm* c, const ldnn_exchange* x, int num_rings, void* stream);
 /* compat gossip: out = c_self*x + sum_d c_d * x[(r-d) mod ws], d in offsets (1 or 2 entries) */
 int ldnn_gossip_pull(const ldnn_comm* c, void* const* bufs /*symmetric fp32*/, void* const* recv /*symmetric*/,
                      long long n, float c_self, int n_off, const int* offsets, const float* coefs, void* stream);

@@ -52,7 +52,8 @@ class Exchange(C.Structure):
     _fields_ = [("grads", C.c_void_p * MAX_RANKS), ("params", C.c_void_p * MAX_RANKS),
                 ("recv", C.c_void_p * MAX_RANKS), ("m", C.c_void_p), ("v", C.c_void_p), ("shadow", C.c_void_p),
                 ("n", C.c_longlong), ("weight", C.c_float * MAX_RANKS), ("self_coef", C.c_float), ("mode", C.c_int),
-                ("opt", Optim)]
+                ("opt", Optim), ("ll", C.c_void_p * MAX_RANKS), ("ll_phase4", C.c_longlong),
+                ("ll_clear4", C.c_longlong), ("ll_epoch", C.c_uint)]
 
 
 X_UPDATE, X_SELFMIX, X_CAST = 1, 2, 4
@@ -79,6 +80,8 @@ def lib():
         _lib = C.CDLL(LIB_PATH)
         _lib.ldnn_last_error.restype = C.c_char_p
         _lib.ldnn_launch_count.restype = C.c_ulonglong
+        _lib.ldnn_ring_ll_slots.restype = C.c_longlong
+        _lib.ldnn_ring_ll_slots.argtypes = [C.c_longlong, C.c_int, C.c_int]
     return _lib
 
 

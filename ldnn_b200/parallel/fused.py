@@ -12,6 +12,8 @@ allreduce      (always global)      ``ldnn_allreduce_fused`` two-shot: pull-redu
 ring           allreduce            ``ldnn_ring_fused(num_rings=1)`` RS+AG around one ring
 double_ring    allreduce            ``ldnn_ring_fused(num_rings=2)`` two counter-rotating rings,
                                     each on half of the slab
+ring / dring   allreduce, <= 32 MB  ``ldnn_ring_ll``: the same RS+AG schedule, flag-free (payload
+                                    announces itself in a sentinel-initialised staging pad)
 ring / dring   gossip (reference)   ``ldnn_gossip_pull`` 1-/2-hop neighbour mix, out of place
 =============  ===================  =========================================================
 
@@ -27,6 +29,7 @@ every topology when ``semantics == "allreduce"``.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional
 
 import torch
@@ -36,7 +39,16 @@ from ..ops import _lib as L
 from ..ops import native_ops as K
 from .exchange import ExchangeSpec, gossip_coefficients, reduce_form
 
-SM_CLOCK_KHZ = 1_900_000
+SM_CLOCK_KHZ = 1_965_000       # fallback when the device does not report a clock (B200 max SM clock)
+
+
+def _sm_clock_khz(device) -> int:
+    """SM clock the watchdog's cycle budget is derived from (cudaDevAttrClockRate, kHz)."""
+    try:
+        khz = int(getattr(torch.cuda.get_device_properties(device), "clock_rate", 0))
+    except Exception:
+        khz = 0
+    return khz if khz > 0 else SM_CLOCK_KHZ
 
 
 class SymmetricBuffer:
@@ -46,6 +58,8 @@ class SymmetricBuffer:
         self.name, self.nbytes = name, nbytes
         self.ptrs: List[int] = [0] * rt.world_size
         self.ptrs[rt.rank] = local_ptr
+        self.rank, self.device = rt.rank, rt.device
+        self._ipc_opened: List[int] = []    # peer mappings this object opened through CUDA IPC (ours to close)
         self.multicast = 0             # multicast address of the slab (NVLS), 0 = none
         if handle is None and rt.world_size > 1:
             # slab from torch's symmetric-memory allocator (LDNN_NVLS=1): peers + multicast from its rendezvous
@@ -60,6 +74,22 @@ class SymmetricBuffer:
             for r, h in enumerate(handles):
                 if r != rt.rank:
                     self.ptrs[r] = K.symm_open(h, nbytes, rt.device)
+                    self._ipc_opened.append(self.ptrs[r])
+
+    def close_peers(self) -> None:
+        """Drop this object's mappings of the peers' slabs (reference-counted by the driver: another exchanger over
+        the same slab keeps its own)."""
+        with torch.cuda.device(self.device):
+            for p in self._ipc_opened:
+                L.check(L.lib().ldnn_symm_close(C.c_void_p(p)))
+        self._ipc_opened = []
+
+    def free_local(self) -> None:
+        """Free the local slab (only for slabs the exchanger allocated itself; call after every peer unmapped it)."""
+        p, self.ptrs[self.rank] = self.ptrs[self.rank], 0
+        if p:
+            with torch.cuda.device(self.device):
+                L.check(L.lib().ldnn_symm_free(C.c_void_p(p)))
 
     def table(self):
         arr = (C.c_void_p * L.MAX_RANKS)()
@@ -79,7 +109,14 @@ class FusedExchanger:
         # measured on 4 and 8 B200 (tools/gpu_tune_overlap.sh): the two-shot kernel saturates NVLink with 32
         # CTAs and leaves more SMs to the overlapped backward; the rings want 64
         self.blocks = comm_blocks or (32 if spec.topology == "allreduce" else 64)
-        self.timeout_cycles = int(watchdog_ms * SM_CLOCK_KHZ)
+        # the exchange CTAs spin on their peers and are launched non-cooperatively next to the backward kernels: every
+        # one of them must be resident at once on every rank, so the grid never exceeds half of the SMs
+        try:
+            sms = int(torch.cuda.get_device_properties(rt.device).multi_processor_count)
+        except Exception:
+            sms = 148
+        self.blocks = max(1, min(self.blocks, sms // 2))
+        self.timeout_cycles = int(watchdog_ms * _sm_clock_khz(rt.device))
         self.epoch = 0
         self.launches = 0
         dev = rt.device
@@ -94,6 +131,11 @@ class FusedExchanger:
         self._signal_t = t
         self._bufs["signal"] = SymmetricBuffer("signal", p, h, L.SIGNAL_WORDS * 4, rt)
         self._recv = None
+        # flag-free ring path (ldnn_ring_ll) for payloads up to LDNN_RING_LL_MAX_MB (0 disables it)
+        self.ll_max_bytes = int(float(os.environ.get("LDNN_RING_LL_MAX_MB", "32")) * (1 << 20))
+        self._ll = None
+        self._ll_epoch = 0              # ldnn_ring_ll calls issued on the pad so far (identical on every rank)
+        self._ll_prev_used = 0          # slots the previous call used (re-armed by the next one)
         self.error_flag = torch.zeros(1, dtype=torch.int32, device=dev)
         self.n = engine.flat.total
         if self.world > 1:
@@ -109,6 +151,24 @@ class FusedExchanger:
             if self.world > 1:
                 dist.barrier()
         return self._recv
+
+    def _ll_buf(self) -> SymmetricBuffer:
+        """Staging pad of the flag-free rings: 3 phases, every word = the sentinel 0x80000000 (-0.0f)."""
+        if self._ll is None:
+            self._ll_phase4 = 2 * (self.ll_max_bytes // 16) + 4096
+            nbytes = 3 * self._ll_phase4 * 16
+            t, h, p = K.symm_alloc(nbytes, self.rt.device)
+            t.view(torch.int32).fill_(-2 ** 31)
+            torch.cuda.synchronize(self.rt.device)
+            self._ll_t = t
+            self._ll = SymmetricBuffer("ll", p, h, nbytes, self.rt)
+            if self.world > 1:
+                dist.barrier()
+        return self._ll
+
+    def _use_ll(self, e: L.Exchange) -> bool:
+        return (self.world > 1 and self.spec.topology != "allreduce" and not (e.mode & L.X_SELFMIX)
+                and 0 < e.n * 4 <= self.ll_max_bytes)
 
     def _comm(self) -> L.Comm:
         self.epoch += 1
@@ -167,7 +227,16 @@ class FusedExchanger:
             L.check(lib.ldnn_allreduce_fused(C.byref(c), C.byref(e), st))
         else:
             rings = 1 if self.spec.topology == "ring" else 2
-            L.check(lib.ldnn_ring_fused(C.byref(c), C.byref(e), rings, st))
+            if self._use_ll(e):
+                tab = self._ll_buf().table()
+                for i in range(self.world):
+                    e.ll[i] = tab[i]
+                e.ll_phase4, e.ll_clear4, e.ll_epoch = self._ll_phase4, self._ll_prev_used, self._ll_epoch % 3
+                L.check(lib.ldnn_ring_ll(C.byref(c), C.byref(e), rings, st))
+                self._ll_epoch += 1
+                self._ll_prev_used = int(lib.ldnn_ring_ll_slots(C.c_longlong(e.n), self.world, rings))
+            else:
+                L.check(lib.ldnn_ring_fused(C.byref(c), C.byref(e), rings, st))
         self.launches += 1
 
     def _gossip(self, data: str) -> None:
@@ -335,6 +404,29 @@ class FusedExchanger:
             raise L.LdnnError("exchange watchdog expired: a peer did not reach the flag in time")
 
     def close(self) -> None:
+        """Collective.  Unmaps the peers' slabs and frees what this exchanger allocated (signal pad, staging slabs,
+        metric table); the engine's parameter/gradient slabs stay with the engine.  Order: everyone idle -> everyone
+        unmaps -> everyone frees (freeing memory a peer still maps is the failure mode)."""
+        if getattr(self, "_closed", False):
+            return
+        self._closed = True
         torch.cuda.synchronize(self.rt.device)
         if self.world > 1:
             dist.barrier()
+        own = [b for b in (self._bufs.get("signal"), self._recv, self._ll, getattr(self, "_met", None)) if b is not None]
+        try:
+            for b in list(self._bufs.values()) + own[1:]:
+                b.close_peers()
+            if self.world > 1:
+                dist.barrier()
+            for name in ("_signal_t", "_recv_t", "_ll_t", "_met_t"):      # non-owning views of the slabs
+                if hasattr(self, name):
+                    setattr(self, name, None)
+            for b in own:
+                b.free_local()
+        except L.LdnnError as err:                                          # teardown must not take a run down
+            import warnings
+            warnings.warn(f"FusedExchanger.close: {err}")
+        self._recv = self._ll = None
+        if hasattr(self, "_met"):
+            del self._met
