@@ -25,7 +25,8 @@ extern std::atomic<unsigned long long> g_launches;
 
 constexpr int kCommThreads = 512;
 constexpr int kBarWords = 512 * LDNN_MAX_RANKS;        // barrier slots: [block][src rank]
-constexpr int kFlagWords = LDNN_SIGNAL_WORDS - kBarWords;
+constexpr int kUserWords = 64;                          // tail of the pad: host-visible flag words (straggler limit)
+constexpr int kFlagWords = LDNN_SIGNAL_WORDS - kBarWords - kUserWords;
 
 struct Peers { void* p[LDNN_MAX_RANKS]; };
 
@@ -292,7 +293,8 @@ allreduce_nvls_kernel(const ldnn_comm c, const ldnn_exchange e, float4* const mc
 //   k = W-1        : wait(W-2); c = c0+1 is fully reduced here: (optimizer) -> own slab, -> next slab
 //   W <= k <= 2W-3 : wait(k-1); forward the finished chunk c = c0-k+W from own slab -> next slab
 //   end            : wait(2W-3) (last chunk has landed), bf16 cast of what arrived
-// Flags: sig[kBarWords + ((ring*J + j) * 16 + k)] in the CONSUMER's pad, value = this call's sequence.
+// Flags: ONE word per chain, sig[kBarWords + ring*J + j] in the CONSUMER's pad; the hops of a chain are strictly
+// sequential, so the word just counts them: value = epoch*64 + k + 1 after message k (never reset, wrap-safe compare).
 //
 // A CTA is four independent GROUPS of 128 threads (named barriers 1..4).  Every hop of a sub-chunk ends in
 // "all stores issued -> system-scope release -> flag", during which its issuer sends nothing; with four
@@ -339,6 +341,7 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
   unsigned int* const next_flags = x.sig[next] + kBarWords;
   const float wr = e.weight[r];
   const int nmsg = 2 * (W - 1);
+  const unsigned int fseq = c.epoch * 64u;      // chain flag after message k of this call = fseq + k + 1  (k < 16)
   bool alive = true;
 
   for (int k = 0; k <= nmsg && W > 1; ++k) {
@@ -348,9 +351,9 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
     const long long c_lo = min(reg_lo + (long long)cidx * chunk4, reg_hi), c_hi = min(c_lo + chunk4, reg_hi);
     for (int j = gir; j < J; j += groups_per_ring) {
       const long long lo = min(c_lo + (long long)j * sub4, c_hi), hi = min(lo + sub4, c_hi);
-      const int fidx = (ring * J + j) * 16;
+      const int fidx = ring * J + j;
       if (k > 0) {
-        if (gt == 0 && alive) alive = spin_until(x, my_flags + fidx + (k - 1), seq + 2);
+        if (gt == 0 && alive) alive = spin_until(x, my_flags + fidx, fseq + (unsigned int)k);
         group_sync(grp);
       }
       constexpr int U = 4;
@@ -394,7 +397,7 @@ ring_fused_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings,
         // the group's stores happen-before thread 0's release through the barrier; st.release.sys then orders
         // them (cumulatively) before the flag for the acquiring consumer
         group_sync(grp);
-        if (gt == 0) st_release_sys(next_flags + fidx + k, seq + 2);
+        if (gt == 0) st_release_sys(next_flags + fidx, fseq + (unsigned int)k + 1u);
       }
     }
   }
@@ -498,17 +501,20 @@ ring_ll_kernel(const ldnn_comm c, const ldnn_exchange e, const int num_rings) {
     constexpr int U = 4;                       // elements per thread in flight: polls and stores of a batch overlap
     for (long long base = (long long)x.block * tpr + t; base < len; base += (long long)U * x.blocks * tpr) {
       float4 a[U], g[U];
+      // first probe of every slot of the batch and the local gradient loads go out together; in steady state the
+      // upstream rank is a whole step ahead, so the probes hit and the spin loop below is not entered
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const long long l = base + (long long)u * x.blocks * tpr;
         if (l >= len) continue;
+        if (k > 0) a[u] = ld_sys_f4(my_pad + (long long)(k - 1) * slot4 + l);
         if (k < W) g[u] = gr[c_lo + l];
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const long long l = base + (long long)u * x.blocks * tpr;
         if (l >= len) continue;
-        if (k > 0) {
+        if (k > 0 && (is_sentinel(a[u].x) | is_sentinel(a[u].y) | is_sentinel(a[u].z) | is_sentinel(a[u].w))) {
           if (alive) alive = poll_slot(x, my_pad + (long long)(k - 1) * slot4 + l, a[u]);
           if (!alive) a[u] = make_float4(0, 0, 0, 0);
         }
@@ -704,13 +710,14 @@ extern "C" int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int n
   LDNN_ARG(c->world == 1 || x->recv[c->emulate ? 0 : c->rank] != nullptr, "ring: needs the symmetric `recv` staging slab");
   const long long n4 = x->n / 4;
   const long long chunk4 = (n4 / num_rings + c->world) / c->world + 1;
-  // sub-chunks: one per hand-off chain.  Every group of 128 threads runs its own chain (4 per CTA), so a payload is cut
-  // into ~2 sub-chunks per group per step, never shorter than 16 KB (a hand-off costs a system-scope release + a flag
-  // round trip); the flag table caps J
+  // sub-chunks: one per hand-off chain.  Every group of 128 threads runs its own chains (4 groups per CTA).  Under load
+  // a hand-off (system-scope release + flag + the consumer's poll) costs ~13 us, during which the chain is idle: a group
+  // therefore owns ~8 chains per step, so that it always has another sub-chunk to stream while hand-offs are in flight.
+  // Never shorter than 4 KB (2 x 16 B per thread); the flag table (one word per chain) caps J.
   const int gpr = std::max(1, c->blocks * kGroups / num_rings);
-  long long sub4 = std::max<long long>(1024, (chunk4 + 2 * gpr - 1) / (2 * gpr));
+  long long sub4 = std::max<long long>(256, (chunk4 + 8 * gpr - 1) / (8 * gpr));
   int J = (int)((chunk4 + sub4 - 1) / sub4);
-  const int maxJ = kFlagWords / (16 * 2);
+  const int maxJ = kFlagWords / 2;
   if (J > maxJ) { J = maxJ; sub4 = (chunk4 + J - 1) / J; }
   if (J < 1) J = 1;
   return launch_comm(ring_fused_kernel, *c, (cudaStream_t)stream, *c, *x, num_rings, J, sub4);

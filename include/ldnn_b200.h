@@ -220,6 +220,9 @@ typedef struct {
   unsigned int debug_delay_cycles;
 } ldnn_comm;
 #define LDNN_SIGNAL_WORDS 65536
+/* pad layout (uint32 words): [0, 4096) barrier slots [block][rank] | [4096, 65472) ring chain flags |
+ * [65472, 65536) user flag words, never touched by the kernels (the trainer's straggler announcements) */
+#define LDNN_SIGNAL_USER_BASE (LDNN_SIGNAL_WORDS - 64)
 
 /* mode bits for the exchange kernels */
 #define LDNN_X_UPDATE 1   /* run the optimizer on the reduced gradient (fused tail) */

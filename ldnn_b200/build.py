@@ -36,6 +36,22 @@ def _digest() -> str:
     return h.hexdigest()
 
 
+def needs_build() -> bool:
+    """True when the library is missing or older than csrc/ + include/ (digest stamp).  Without nvcc (a box that only
+    received the built .so) an existing library is used as it is."""
+    stamp = os.path.join(LIBDIR, "build.stamp")
+    if not os.path.exists(LIB):
+        return True
+    try:
+        _nvcc()
+    except RuntimeError:
+        return False
+    try:
+        return not (os.path.exists(stamp) and open(stamp).read() == _digest())
+    except OSError:
+        return False
+
+
 def build(force: bool = False, verbose: bool = True) -> str:
     os.makedirs(LIBDIR, exist_ok=True)
     os.makedirs(OBJDIR, exist_ok=True)
@@ -56,10 +72,12 @@ def build(force: bool = False, verbose: bool = True) -> str:
 
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         objs = list(ex.map(compile_one, srcs))
-    cmd = [nvcc] + ARCH + ["-shared", "-o", LIB] + objs + ["-lcudart_static", "-ldl", "-lrt", "-lpthread"]
+    tmp_lib = f"{LIB}.{os.getpid()}.tmp"          # link beside the target, then rename: readers never see a partial file
+    cmd = [nvcc] + ARCH + ["-shared", "-o", tmp_lib] + objs + ["-lcudart_static", "-ldl", "-lrt", "-lpthread"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    os.replace(tmp_lib, LIB)
     with open(stamp, "w") as f:
         f.write(dig)
     if verbose:

@@ -17,7 +17,7 @@ from .config import Config, parse_args
 from .engine import make_engine
 from .launch import init_runtime, shutdown
 from .parallel import make_exchanger
-from .trainer import TrainHistory, evaluate, train_global
+from .trainer import TrainHistory, evaluate, refresh_shard_weights, train_global
 from .utils import checkpoint as ckpt
 from .utils import viz
 
@@ -51,16 +51,14 @@ def _run_traced(cfg: Config, rt, phase) -> TrainHistory:
     exchanger.broadcast_state(engine, src=0)
 
     shards = D.initial_shards(bundle, cfg, rt, engine)
-    if cfg.aggregation_type == "shard":
-        # shard-weighted averaging: w_r = n_r / Σn from the actual shard sizes
-        sizes = D.all_gather_floats(float(len(shards.train_indices)), rt)
-        exchanger.set_shard_weights([s / max(sum(sizes), 1.0) for s in sizes])
+    refresh_shard_weights(cfg, rt, shards, exchanger)      # shard-weighted averaging: w_r = n_r / Σn
 
     history = TrainHistory()
     start_epoch = 0
     if cfg.resume:
         start_epoch = ckpt.load_checkpoint(cfg.resume, engine, history, shards, rank=rt.rank, world_size=rt.world_size)
         engine.params_changed()
+        refresh_shard_weights(cfg, rt, shards, exchanger)  # the checkpoint may have restored different shards
 
     def on_epoch_end(ge, h, sh):
         if cfg.save:
@@ -68,6 +66,8 @@ def _run_traced(cfg: Config, rt, phase) -> TrainHistory:
             everyone = ckpt.gather_shards(sh, rt)  # collective: each rank trains on its own shard
             if rt.rank == 0:
                 ckpt.save_checkpoint(cfg.save, engine, h, sh, epoch=ge + 1, cfg=cfg, all_shards=everyone)
+            else:                                  # replicas differ between exchanges (and BN buffers always do)
+                ckpt.save_rank_state(cfg.save, engine, rt.rank, rt.world_size, epoch=ge + 1)
 
     history = train_global(engine, bundle, shards, cfg, rt, exchanger, history, start_epoch, on_epoch_end)
 

@@ -213,7 +213,7 @@ def make_train_global(topology: str, balance: str):
         bundle = D.DataBundle(trainset, valset, valset, int(trainset.labels.max()) + 1 if len(trainset) else 10, "user")
         shards = D.ShardState(np.asarray(indices_train), np.asarray(indices_val),
                               [1.0 / world_size] * world_size, fixed_classes)
-        ex = DistExchanger(ExchangeSpec.from_config(cfg, world_size), rank)
+        ex = CompatExchanger(ExchangeSpec.from_config(cfg, world_size), rank)     # fused P2P kernels on a GPU job
         return T.train_global(eng, bundle, shards, cfg, rt, ex).as_tuple()
 
     return train_global
@@ -222,10 +222,27 @@ def make_train_global(topology: str, balance: str):
 # ---------------------------------------------------------------------------
 # communication.py surface
 # ---------------------------------------------------------------------------
+class CompatExchanger(DistExchanger):
+    """The exchanger behind the reference-signature entry points.  On a single-node GPU job every exchange of an fp32
+    CUDA tensor runs on the hand-written P2P kernels (staged through a symmetric slab, `StagedFusedExchange`) — the
+    variant directories' ``communication.py`` / ``trainer.py`` are product paths, not NCCL calls.  CPU tensors, other
+    dtypes and multi-node jobs take the torch.distributed realisation it inherits (`LDNN_COMPAT_DIST=1` forces it)."""
+
+    @torch.no_grad()
+    def exchange_(self, t: torch.Tensor) -> torch.Tensor:
+        if self.spec.world_size > 1 and self.group is None:
+            from .parallel.fused import StagedFusedExchange
+            dev = t.device
+            if StagedFusedExchange.usable(None, t):
+                rt = _runtime(dev, self.rank, self.spec.world_size)
+                return StagedFusedExchange.get(rt).exchange_(t, self.spec)
+        return super().exchange_(t)
+
+
 def _ex(topology, kind, world_size, local_weight=0.5, rank=None):
     r = rank if rank is not None else (dist.get_rank() if dist.is_initialized() else 0)
     sem = "allreduce" if topology == "allreduce" else "gossip"
-    return DistExchanger(ExchangeSpec(topology, sem, kind, local_weight, None, world_size), r)
+    return CompatExchanger(ExchangeSpec(topology, sem, kind, local_weight, None, world_size), r)
 
 
 def _each(model, what):

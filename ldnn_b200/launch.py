@@ -51,10 +51,28 @@ class Runtime:
         return self._single_node
 
 
+def launcher_env(env=None):
+    """(rank, world size, local rank) from whichever launcher started this process.
+
+    torchrun / torch.distributed.launch set RANK / WORLD_SIZE / LOCAL_RANK.  The reference's four ring variants are
+    started as ``mpirun -n N python main.py`` (Balanced Ring/main.py:11-18 reads MPI.COMM_WORLD), so the variables of
+    the common MPI launchers are understood too — Open MPI (OMPI_COMM_WORLD_*), MPICH / Intel MPI / Hydra (PMI_*),
+    Slurm's srun (SLURM_PROCID, SLURM_NTASKS, SLURM_LOCALID) — and an existing `mpirun` line keeps working: the ranks
+    rendezvous over torch.distributed at MASTER_ADDR:MASTER_PORT (127.0.0.1:29500 unless set; one host by default)."""
+    env = os.environ if env is None else env
+    for rk, wk, lk in (("RANK", "WORLD_SIZE", "LOCAL_RANK"),
+                       ("OMPI_COMM_WORLD_RANK", "OMPI_COMM_WORLD_SIZE", "OMPI_COMM_WORLD_LOCAL_RANK"),
+                       ("PMI_RANK", "PMI_SIZE", "MPI_LOCALRANKID"),
+                       ("PMIX_RANK", "PMIX_SIZE", "PMIX_LOCAL_RANK"),
+                       ("SLURM_PROCID", "SLURM_NTASKS", "SLURM_LOCALID")):
+        if rk in env and wk in env:
+            rank, world = int(env[rk]), int(env[wk])
+            return rank, world, int(env.get(lk, str(rank)))
+    return 0, 1, 0
+
+
 def init_runtime(backend: str = "gloo", seed=None, force_cpu: bool = False) -> Runtime:
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", str(rank)))
+    rank, world, local_rank = launcher_env()
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29500")
 

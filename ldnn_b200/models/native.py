@@ -495,9 +495,9 @@ class _StepPlan:
             geo, xin = (n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad), self.act[u.src]
         bn_, sp_, lt_ = K.tuned_conv_config(
             K.FPROP, geo, lambda b, s_, l_: K.ConvPlan(K.FPROP, *geo, xin, w, yraw, bn_sums=fsum, block_n=b, splits=s_,
-                                                       lite=l_), eng.autotune, eng.dcode)
+                                                       **K.variant_kwargs(l_)), eng.autotune, eng.dcode)
         plan = K.ConvPlan(K.FPROP, *geo, xin, w, yraw, workspace=self.ws, bn_sums=fsum, block_n=bn_, splits=sp_,
-                          lite=lt_)
+                          **K.variant_kwargs(lt_))
         self._add(plan.run, plan.num_launches)
         if fast:
             self._add(lambda: K.bn_fwd_apply_sums(yraw, fsum, gamma, beta, rm, rv, nbt, sm, si, res, out, M, Cc, u.relu,
@@ -550,10 +550,11 @@ class _StepPlan:
         atomic = not eng.deterministic
         bn_, sp_, lt_ = K.tuned_conv_config(
             K.WGRAD, geo, lambda b, s_, l_: K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, atomic_out=atomic,
-                                                       block_n=b, splits=s_, lite=l_), eng.autotune and atomic,
+                                                       block_n=b, splits=s_, **K.variant_kwargs(l_)),
+            eng.autotune and atomic,
             eng.dcode)
         wg = K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, workspace=self.ws, atomic_out=atomic, block_n=bn_,
-                        splits=sp_, lite=lt_)
+                        splits=sp_, **K.variant_kwargs(lt_))
         if atomic and K.conv_query(K.WGRAD, *geo, block_n=bn_, splits=sp_, dtype=eng.dcode)[0] > 0:   # split-K → red.add into a zeroed slice
             sl = eng.flat.by_key[u.conv_key + ".weight"]
             self.zero_ranges.append((sl.offset, sl.offset + sl.numel))
@@ -569,7 +570,7 @@ class _StepPlan:
             acc = True
         bn_, sp_, lt_ = K.tuned_conv_config(
             K.DGRAD, geo, lambda b, s_, l_: K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx, accumulate=True, block_n=b,
-                                                       splits=s_, lite=l_), eng.autotune, eng.dcode)
+                                                       splits=s_, **K.variant_kwargs(l_)), eng.autotune, eng.dcode)
         fuse = None
         if u.conv_key in self.fuse_into:
             ow = self.fuse_into[u.conv_key]
@@ -578,7 +579,7 @@ class _StepPlan:
                     eng.save_invstd[oo:oo + ow.cout],
                     eng.bn_sums[2 * eng.c_tot + 2 * oo:2 * eng.c_tot + 2 * oo + 2 * ow.cout], ow.relu)
         dg = K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx if acc else None, accumulate=acc, workspace=self.ws,
-                        block_n=bn_, splits=sp_, bn_bwd_fuse=fuse, lite=lt_)
+                        block_n=bn_, splits=sp_, bn_bwd_fuse=fuse, **K.variant_kwargs(lt_))
         self._add(dg.run, dg.num_launches)
         written.add(u.src)
 

@@ -67,14 +67,31 @@ def available() -> bool:
     return shutil.which("nvcc") is not None or os.path.exists("/usr/local/cuda/bin/nvcc")
 
 
+def _ensure_built() -> None:
+    """In-tree build on first use (nvcc needed, ~1 min), safe when N ranks start together: one process builds under an
+    exclusive file lock while the others wait; `build()` itself compares the source digest with the stamp (so a stale
+    library is rebuilt after csrc/ changes) and installs the new .so with an atomic rename."""
+    import fcntl
+    from ..build import build as _build, needs_build
+    if not needs_build():
+        return
+    os.makedirs(os.path.dirname(LIB_PATH), exist_ok=True)
+    with open(os.path.join(os.path.dirname(LIB_PATH), ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if needs_build():                      # another rank may have finished while we waited
+                _build(verbose=False)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
 def lib():
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            try:                                   # in-tree build on first use (nvcc needed, ~30 s)
-                from ..build import build as _build
-                _build(verbose=False)
-            except Exception as e:
+        try:
+            _ensure_built()
+        except Exception as e:
+            if not os.path.exists(LIB_PATH):
                 raise LdnnError(f"{LIB_PATH} is missing and could not be built ({e}) — run "
                                 f"`python -m ldnn_b200.build` (or __graft_entry__.build())")
         _lib = C.CDLL(LIB_PATH)

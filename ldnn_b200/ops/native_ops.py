@@ -123,7 +123,7 @@ def load_tune_cache(path=None):
             key = tuple(int(v) for v in ks.split(","))
             if len(key) == 9:                     # round-1 files: (mode, geometry) of the bf16 kernels
                 key = (0,) + key
-            _TUNE_CACHE.setdefault(key, (int(cfg[0]), int(cfg[1]), bool(cfg[2])))
+            _TUNE_CACHE.setdefault(key, (int(cfg[0]), int(cfg[1]), int(cfg[2])))
             n += 1
         except (ValueError, IndexError, TypeError):
             continue
@@ -135,7 +135,7 @@ def save_tune_cache(path=None):
     path = path or _tune_file()
     if not path:
         return False
-    blob = {"version": 2, "key": "dtype(0 bf16, 1 tf32),mode,N,H,W,Cin,Cout,R,stride,pad", "configs": {_tune_key_str(k): [c[0], c[1], bool(c[2])] for k, c in sorted(_TUNE_CACHE.items())}}
+    blob = {"version": 2, "key": "dtype(0 bf16, 1 tf32),mode,N,H,W,Cin,Cout,R,stride,pad", "configs": {_tune_key_str(k): [c[0], c[1], int(c[2])] for k, c in sorted(_TUNE_CACHE.items())}}
     tmp = f"{path}.{os.getpid()}.tmp"
     try:
         with open(tmp, "w") as f:
@@ -172,10 +172,22 @@ def conv_candidates(mode, geo, n_total):
     return out
 
 
+# launch variants of the conv kernel the tuner chooses between (third field of a tuned config)
+V_FULL, V_LITE, V_MCAST, V_PAIR = 0, 1, 2, 3
+
+
+def variant_kwargs(variant) -> dict:
+    """ConvPlan keyword arguments of a tuned variant: 0 full pipeline, 1 lite (two CTAs per SM), 2 clusters of two
+    M tiles with the weight tile TMA-multicast, 3 CTA pairs running one tcgen05.mma.cta_group::2 (UMMA_M = 256)."""
+    v = int(variant)
+    return {"lite": v == V_LITE, "cluster": {V_MCAST: 2, V_PAIR: -2}.get(v, 1)}
+
+
 def tuned_conv_config(mode, geo, make_plan, enabled=True, dtype=0):
-    """Returns (block_n, splits, lite) — (0, 0, False) = library heuristics.  `make_plan(block_n,
-    splits, lite)` must build a runnable plan (private scratch) for timing.  `lite` (two CTAs per SM)
-    is tried only for grids of more than one wave.  `dtype`: 0 bf16, 1 tf32 (separate tunings)."""
+    """Returns (block_n, splits, variant) — (0, 0, 0) = library heuristics.  `make_plan(block_n, splits, variant)`
+    must build a runnable plan (private scratch) for timing; see `variant_kwargs`.  `lite` is tried only for
+    grids of more than one wave, the cluster / pair forms for 128- and 256-wide tiles of fprop and dgrad.
+    `dtype`: 0 bf16, 1 tf32 (separate tunings)."""
     global _TUNE_FILE_LOADED
     key = (int(dtype), int(mode)) + tuple(int(v) for v in geo)
     if not _TUNE_FILE_LOADED:
@@ -184,29 +196,32 @@ def tuned_conv_config(mode, geo, make_plan, enabled=True, dtype=0):
         if not os.environ.get("LDNN_NO_TUNE_DEFAULTS"):
             load_tune_cache(DEFAULT_TUNE_FILE)
     if not enabled:                                # no timing runs; known tunings are still replayed
-        return _TUNE_CACHE.get(key, (0, 0, False))
+        return _TUNE_CACHE.get(key, (0, 0, 0))
     if key in _TUNE_CACHE:
         return _TUNE_CACHE[key]
     N, H, W, Cin, Cout, R, stride, pad = geo
     n_total = Cout if mode == FPROP else Cin
-    base = make_plan(0, 0, False)
-    best_cfg, best_t = (0, 0, False), _time_plan(base)
-    seen = {(0, base.grid, False)}
+    base = make_plan(0, 0, V_FULL)
+    best_cfg, best_t = (0, 0, V_FULL), _time_plan(base)
+    seen = {(0, base.grid, V_FULL)}
     cands = [(0, 0)] + conv_candidates(mode, geo, n_total)
+    variants = (V_FULL, V_LITE) if mode == WGRAD else (V_FULL, V_LITE, V_PAIR, V_MCAST)
     for bn, sp in cands:
-        for lite in (False, True):
+        for var in variants:
+            if var in (V_PAIR, V_MCAST) and bn < 128:
+                continue
             try:
-                plan = make_plan(bn, sp, lite)
+                plan = make_plan(bn, sp, var)
             except L.LdnnError:
                 continue
             ctas = plan.grid[0] * plan.grid[1] * plan.grid[2]
-            sig = (bn, plan.grid, lite)
-            if sig in seen or not (24 <= ctas <= 20000) or (lite and ctas < 296) or (ctas > 1200 and sp > 1):
+            sig = (bn, plan.grid, var)
+            if sig in seen or not (24 <= ctas <= 20000) or (var == V_LITE and ctas < 296) or (ctas > 1200 and sp > 1):
                 continue
             seen.add(sig)
             t = _time_plan(plan)
             if t < best_t * 0.95:                  # only leave the heuristic for a clear win
-                best_cfg, best_t = (bn, sp, lite), t
+                best_cfg, best_t = (bn, sp, var), t
     _TUNE_CACHE[key] = best_cfg
     save_tune_cache()
     return best_cfg
@@ -350,12 +365,21 @@ def symm_alloc(nbytes: int, device):
 
 
 def nvls_requested() -> bool:
-    """`LDNN_NVLS=1`: keep the exchanged slabs in multicast-capable symmetric memory and use the in-switch
-    all-reduce (`ldnn_allreduce_nvls`) where its preconditions hold.  Staged in round 1 (opt-in)."""
-    if not os.environ.get("LDNN_NVLS"):
+    """Keep the exchanged slabs in multicast-capable symmetric memory so that the all-reduce can run inside NVSwitch
+    (`ldnn_allreduce_nvls`: multimem.ld_reduce + multimem.st) where its preconditions hold (uniform weights).
+    Measured on 8 x B200: 752 / 802 / 827 GB/s bus bandwidth at 128 / 256 / 512 MB against 598 / 624 / 640 for the
+    two-shot P2P kernel and 561 / 605 / 587 for NCCL (profiles/exchange_sweep_8gpu_r2.txt) — so it is ON by default for
+    multi-rank single-node jobs; `LDNN_NVLS=0` keeps plain CUDA-IPC slabs (two-shot kernel), `LDNN_NVLS=1` forces the
+    attempt.  A host without multicast support falls back to the IPC slabs by itself."""
+    env = os.environ.get("LDNN_NVLS", "")
+    if env == "0":
         return False
     import torch.distributed as dist
-    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+        return False
+    if env:
+        return True
+    return dist.get_backend() == "nccl"            # auto: GPU jobs only (gloo/CPU jobs have no peer memory)
 
 
 def symm_alloc_multicast(nbytes: int, device):

@@ -12,7 +12,7 @@ allreduce      (always global)      ``ldnn_allreduce_fused`` two-shot: pull-redu
 ring           allreduce            ``ldnn_ring_fused(num_rings=1)`` RS+AG around one ring
 double_ring    allreduce            ``ldnn_ring_fused(num_rings=2)`` two counter-rotating rings,
                                     each on half of the slab
-ring / dring   allreduce, <= 32 MB  ``ldnn_ring_ll``: the same RS+AG schedule, flag-free (payload
+ring / dring   allreduce, <= 64 MB  ``ldnn_ring_ll``: the same RS+AG schedule, flag-free (payload
                                     announces itself in a sentinel-initialised staging pad)
 ring / dring   gossip (reference)   ``ldnn_gossip_pull`` 1-/2-hop neighbour mix, out of place
 =============  ===================  =========================================================
@@ -131,8 +131,9 @@ class FusedExchanger:
         self._signal_t = t
         self._bufs["signal"] = SymmetricBuffer("signal", p, h, L.SIGNAL_WORDS * 4, rt)
         self._recv = None
-        # flag-free ring path (ldnn_ring_ll) for payloads up to LDNN_RING_LL_MAX_MB (0 disables it)
-        self.ll_max_bytes = int(float(os.environ.get("LDNN_RING_LL_MAX_MB", "32")) * (1 << 20))
+        # flag-free ring path (ldnn_ring_ll) for payloads up to LDNN_RING_LL_MAX_MB (default 64 = the ring bucket
+        # size of the per-step schedule; 0 disables it).  The pad costs 6x that much device memory, allocated on first use
+        self.ll_max_bytes = int(float(os.environ.get("LDNN_RING_LL_MAX_MB", "64")) * (1 << 20))
         self._ll = None
         self._ll_epoch = 0              # ldnn_ring_ll calls issued on the pad so far (identical on every rank)
         self._ll_prev_used = 0          # slots the previous call used (re-armed by the next one)
@@ -393,6 +394,18 @@ class FusedExchanger:
         torch.cuda.current_stream(self.rt.device).synchronize()
         return self._met_t[: self.world * n].view(self.world, n).cpu().numpy()
 
+    # ------------------------------------------------------------------ host-visible flag words (C6)
+    USER_BASE = L.SIGNAL_WORDS - 64
+
+    def flag_views(self):
+        """(my slot in every PEER's signal pad, my own pad's slots [world]) as int32 device tensors: the last 64
+        words of the pad are never touched by the kernels.  A store into a peer view crosses NVLink."""
+        pad = self._bufs["signal"]
+        peers = [K.tensor_from_ptr(pad.ptrs[p] + 4 * (self.USER_BASE + self.rank), 4, torch.int32, self.rt.device)
+                 for p in range(self.world) if p != self.rank]
+        mine = K.tensor_from_ptr(pad.ptrs[self.rank] + 4 * self.USER_BASE, 4 * self.world, torch.int32, self.rt.device)
+        return peers, mine
+
     def barrier(self) -> None:
         c = self._comm()
         L.check(L.lib().ldnn_barrier(C.byref(c), L.stream_ptr()))
@@ -430,3 +443,92 @@ class FusedExchanger:
         self._recv = self._ll = None
         if hasattr(self, "_met"):
             del self._met
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Fused kernels for ARBITRARY CUDA tensors (the reference-signature communication.py / trainer.py entry points)
+# ---------------------------------------------------------------------------------------------------------------
+class _StageEngine:
+    """Engine facade around one symmetric staging slab (what FusedExchanger needs: flat slabs + IPC handles)."""
+
+    def __init__(self, n: int, device):
+        from types import SimpleNamespace
+        self._symm, self.shadow = {}, None
+        self.flat = SimpleNamespace(total=n, m=None, v=None)
+        for name in ("params", "grads"):            # `params` is never exchanged here: a 16-byte stand-in
+            t, h, p = K.symm_alloc((n if name == "grads" else 4) * 4, device)
+            self._symm[name] = (t, h, p, (n if name == "grads" else 4) * 4)
+            setattr(self.flat, name, t.view(torch.float32))
+
+    def symm_handle(self, name):
+        return self._symm[name][1], self._symm[name][2], self._symm[name][3]
+
+    def params_changed(self):
+        pass
+
+
+class StagedFusedExchange:
+    """``exchange_(tensor, spec)`` on the fused P2P kernels for any fp32 CUDA tensor: the tensor is copied into a
+    symmetric staging slab, exchanged there by the topology's kernel (two-shot / rings / gossip pull, exactly the
+    kernels the engines use on their own slabs) and copied back.  This is what the variant directories'
+    ``communication.py`` functions and the reference-signature ``train_global`` run on a single-node GPU job, so those
+    entry points are not an NCCL path.  Collective: every rank must call with the same sizes in the same order (the
+    reference's per-parameter loops do).  The slab grows (collectively) to the largest tensor seen."""
+
+    _instances = {}
+
+    @classmethod
+    def get(cls, rt):
+        key = (str(rt.device), rt.rank, rt.world_size)
+        if key not in cls._instances:
+            cls._instances[key] = cls(rt)
+        return cls._instances[key]
+
+    def __init__(self, rt):
+        self.rt, self.cap, self.eng, self.ex = rt, 0, None, {}
+
+    def _ensure(self, n: int):
+        if n <= self.cap:
+            return
+        for ex in self.ex.values():
+            ex.close()
+        self.ex = {}
+        self.cap = max(1 << 20, 1 << (n - 1).bit_length())
+        self.eng = _StageEngine(self.cap, self.rt.device)
+
+    def _exchanger(self, spec: ExchangeSpec) -> FusedExchanger:
+        if spec.topology not in self.ex:            # CTA budget depends on the topology only
+            self.ex[spec.topology] = FusedExchanger(spec, self.rt, self.eng)
+        ex = self.ex[spec.topology]
+        ex.spec = spec
+        return ex
+
+    @torch.no_grad()
+    def exchange_(self, t: torch.Tensor, spec: ExchangeSpec) -> torch.Tensor:
+        n = t.numel()
+        npad = (n + 3) // 4 * 4
+        self._ensure(npad)
+        slab = self.eng.flat.grads
+        slab[:n].copy_(t.reshape(-1))
+        if npad > n:
+            slab[n:npad].zero_()
+        ex = self._exchanger(spec)
+        ex.n = npad
+        if spec.is_gossip():
+            ex._gossip("grads")
+        else:
+            ex._launch_reduce(ex._exchange_struct("grads", 0))
+        t.copy_(slab[:n].view_as(t))
+        return t
+
+    @classmethod
+    def usable(cls, rt, t: torch.Tensor) -> bool:
+        """Single-node NCCL job, fp32 CUDA tensor, at most LDNN_MAX_RANKS ranks, library present."""
+        if not (t.is_cuda and t.dtype == torch.float32 and dist.is_available() and dist.is_initialized()):
+            return False
+        ws = dist.get_world_size()
+        if ws < 2 or ws > L.MAX_RANKS or dist.get_backend() != "nccl" or os.environ.get("LDNN_COMPAT_DIST"):
+            return False
+        if int(os.environ.get("LOCAL_WORLD_SIZE", str(ws))) != ws:
+            return False
+        return L.available()

@@ -12,8 +12,9 @@ epoch, re-shard, the 12 metric series — with these deliberate differences:
   per-rank record;
 * ``--sync step`` adds the product schedule: every step's gradients go through the
   fused exchange+update kernel instead of a local optimizer step;
-* the straggler flag keeps its wire semantics (MAX-reduced int) but the
-  break decision is taken from gathered data so it cannot deadlock.
+* the straggler limit (``--time_limit``) works: a rank that finishes a local epoch announces it through a
+  peer-visible flag word, the ranks still stepping stop ``time_limit`` s later (``parallel/straggler.py``);
+  upstream's version is unreachable and would deadlock if it fired.
 """
 from __future__ import annotations
 
@@ -48,6 +49,7 @@ class TrainHistory:
     global_epoch_seconds: List[float] = field(default_factory=list)
     global_epoch_samples_per_s: List[float] = field(default_factory=list)
     exchange_ms: List[float] = field(default_factory=list)
+    straggler_cuts: List[List[int]] = field(default_factory=list)   # per local epoch: ranks the time limit cut short
 
     def as_tuple(self):
         return (self.all_workers_losses, self.all_epochs_losses, self.global_epoch_losses,
@@ -61,7 +63,7 @@ class TrainHistory:
 # control-plane gather (K-MET): one record per rank per local epoch
 # ---------------------------------------------------------------------------
 class RecordGather:
-    HEADER = 8  # [n_losses, train_loss, train_acc, val_loss, val_acc, finished, want_break, samples]
+    HEADER = 8  # [n_losses, train_loss, train_acc, val_loss, val_acc, cut short by --time_limit, (unused), samples]
 
     def __init__(self, rt, exchanger=None):
         self.rt = rt
@@ -103,7 +105,7 @@ class RecordGather:
 # local epoch / validation / evaluation
 # ---------------------------------------------------------------------------
 def train_local_epoch(engine, loader: D.Loader, rt, exchanger=None, sync_step: bool = False,
-                      num_steps: Optional[int] = None, by_weights: bool = False):
+                      num_steps: Optional[int] = None, by_weights: bool = False, straggler=None):
     """One pass over the rank's shard (``trainer.py:194-223``).
     Returns (mean loss, accuracy %, per-batch losses, samples).
 
@@ -116,7 +118,7 @@ def train_local_epoch(engine, loader: D.Loader, rt, exchanger=None, sync_step: b
     dev = rt.device
     losses = torch.zeros(n_steps, dtype=torch.float32, device=dev)
     correct = torch.zeros((), dtype=torch.float32, device=dev)
-    total, i = 0, 0
+    total, i, stopped = 0, 0, False
     while i < n_steps:                       # wraps when a common step count exceeds the shard
         for x, y in D.DeviceFeeder(loader, dev):
             if i >= n_steps:
@@ -137,9 +139,15 @@ def train_local_epoch(engine, loader: D.Loader, rt, exchanger=None, sync_step: b
             correct += corr
             total += int(y.shape[0])
             i += 1
-        if len(loader) == 0:
+            if straggler is not None and i < n_steps and straggler.should_stop():
+                stopped = True               # a peer finished this epoch time_limit seconds ago: move on
+                break
+        if len(loader) == 0 or stopped:
             break
+    if straggler is not None and not stopped:
+        straggler.announce()
     engine.scheduler_step()
+    losses = losses[:i]
     host = losses.cpu().numpy()              # the one sync of the epoch
     n_ok = float(correct.item())
     return float(host.mean()), 100.0 * n_ok / max(total, 1), host, total
@@ -209,6 +217,18 @@ def evaluate(engine, loader: D.Loader, rt, num_classes: int = 10, verbose: bool 
     return loss, acc, preds, labels
 
 
+def refresh_shard_weights(cfg, rt, shards: D.ShardState, exchanger):
+    """Shard-weighted averaging uses w_r = n_r / sum(n) of the shards the ranks ACTUALLY hold: call after the
+    initial sharding, after every re-shard (sizes follow ratio x total, which moves with the timing-derived ratios)
+    and after a checkpoint restored different shards.  Collective; returns the weights (None if not shard mode)."""
+    if cfg.aggregation_type != "shard":
+        return None
+    sizes = D.all_gather_floats(float(len(shards.train_indices)), rt)
+    w = [s / max(sum(sizes), 1.0) for s in sizes]
+    exchanger.set_shard_weights(w)
+    return w
+
+
 # ---------------------------------------------------------------------------
 # the global loop
 # ---------------------------------------------------------------------------
@@ -220,6 +240,8 @@ def train_global(engine, bundle: D.DataBundle, shards: D.ShardState, cfg, rt, ex
     if not h.all_workers_losses:
         h.all_workers_losses = [[] for _ in range(ws)]
     g = RecordGather(rt, exchanger)
+    from .parallel.straggler import make_straggler, ticket
+    straggler = make_straggler(cfg, rt, exchanger)
     rng = np.random.default_rng(None if cfg.seed is None else cfg.seed + 1000 + rank)
     sync_step = cfg.sync == "step"
 
@@ -230,21 +252,30 @@ def train_global(engine, bundle: D.DataBundle, shards: D.ShardState, cfg, rt, ex
                               D.chunk_batches_for(cfg, bundle.valset))
         capacity = g.max_int(len(train_loader))
         steps = capacity if sync_step else None      # common step count for the per-step schedule
+        if sync_step and ws > 1 and -g.max_int(-len(train_loader)) == 0:
+            # every step of this schedule is a collective: a rank with nothing to feed it would leave its peers
+            # spinning in the exchange until the watchdog fires.  All ranks see the same minimum and stop together.
+            raise RuntimeError(f"--sync step: at least one rank holds an empty training shard in global epoch {ge + 1} "
+                               f"(this rank: {len(shards.train_indices)} samples, batch {cfg.batch_size}); use a larger "
+                               "dataset, a smaller batch size or less skewed --shard_ratios")
         sums = np.zeros(4, dtype=np.float64)         # train loss/acc, val loss/acc over local epochs
         cur_losses: List[float] = []
         cur_accs: List[float] = []
         t_start = time.time()
-        straggler_t0, samples = None, 0
+        samples = 0
 
         for le in range(cfg.epochs_local):
+            if straggler is not None:
+                straggler.begin(ticket(ge, le))
             with nvtx_range(f"train g{ge} l{le}"):
                 tl, ta, batch_losses, n = train_local_epoch(engine, train_loader, rt, exchanger, sync_step, steps,
-                                                            by_weights=cfg.aggregation_by == "weights")
+                                                            by_weights=cfg.aggregation_by == "weights",
+                                                            straggler=straggler)
+            cut = 1.0 if (straggler is not None and straggler.cut_short) else 0.0
             samples += n
             with nvtx_range("validate"):
                 vl, va = validate(engine, val_loader, rt)
-            want_break = 1.0 if (straggler_t0 is not None and time.time() - straggler_t0 > cfg.time_limit) else 0.0
-            recs = g.gather([len(batch_losses), tl, ta, vl, va, 0.0, want_break, n], batch_losses, capacity)
+            recs = g.gather([len(batch_losses), tl, ta, vl, va, cut, 0.0, n], batch_losses, capacity)
             if rank == 0:
                 pooled = []
                 for r in range(ws):
@@ -263,10 +294,8 @@ def train_global(engine, bundle: D.DataBundle, shards: D.ShardState, cfg, rt, ex
                 print(f"Rank {rank}, Global Epoch {ge + 1}, Local Epoch {le + 1}, Loss: {tl}, Accuracy: {ta}")
                 print(f"Worker {rank}, Global Epoch {ge + 1}, Validation Loss: {vl:.4f}, Validation Accuracy: {va:.2f}%")
             sums += np.array([tl, ta, vl, va])
-            if recs[:, 5].max() >= 1.0 and straggler_t0 is None:
-                straggler_t0 = time.time()
-            if recs[:, 6].max() >= 1.0:              # identical on every rank → collective break
-                break
+            if rank == 0:
+                h.straggler_cuts.append([int(r) for r in range(ws) if recs[r, 5] >= 1.0])
 
         g.max_int(1)                                   # post-loop finish flag (C6)
 
@@ -300,6 +329,7 @@ def train_global(engine, bundle: D.DataBundle, shards: D.ShardState, cfg, rt, ex
         h.global_epoch_seconds.append(dur)
         h.global_epoch_samples_per_s.append(tot_samples / max(dur, 1e-9))
         shards = D.reshard(bundle, shards, cfg, rt, dur, tot_dur, rng)
+        refresh_shard_weights(cfg, rt, shards, exchanger)      # the exchange weights follow the new shard sizes
         if on_epoch_end is not None:
             on_epoch_end(ge, h, shards)
     return h

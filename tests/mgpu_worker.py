@@ -19,6 +19,7 @@ def main():
     from ldnn_b200.parallel.exchange import ExchangeSpec, mixing_matrix
     from ldnn_b200.parallel.fused import FusedExchanger
     from test_flat_optimizer import tiny_spec
+    from ldnn_b200.ops import _lib as L
 
     rt = init_runtime("nccl", seed=0)
     ws, r, dev = rt.world_size, rt.rank, rt.device
@@ -95,6 +96,34 @@ def main():
             assert float((got - want).abs().max()) < 1e-5, (topo, it)
         ex.check()
         ex.close()
+
+    # reference-signature communication.py functions on CUDA tensors of assorted sizes: they run on the fused P2P
+    # kernels (staged through a symmetric slab), and — unlike upstream's ring functions on GPU — they
+    # change the caller's tensor.  Oracle: the variant's mixing matrix.
+    from ldnn_b200 import compat
+    from ldnn_b200.parallel.fused import StagedFusedExchange
+    launched0 = L.launch_count()
+    cases = [("allreduce", "equal", lambda t: compat._ex("allreduce", "equal", ws).exchange_(t)),
+             ("allreduce", "weighted", lambda t: compat._ex("allreduce", "weighted", ws, 0.7).exchange_(t)),
+             ("ring", "equal", lambda t: compat.ring_all_reduce_equal(t, r, ws)),
+             ("ring", "weighted", lambda t: compat.ring_all_reduce_weighted(t, r, ws, 0.7)),
+             ("double_ring", "equal", lambda t: compat.double_ring_all_reduce(t, r, ws)),
+             ("double_ring", "weighted", lambda t: compat.double_ring_all_reduce_weighted(t, r, ws, 0.7))]
+    for topo, kind, fn in cases:
+        sem = "allreduce" if topo == "allreduce" else "gossip"
+        M = torch.from_numpy(mixing_matrix(ExchangeSpec(topo, sem, kind, 0.7, None, ws)))
+        for shape in [(10,), (64, 3, 3, 3), (1024, 1027)]:
+            numel = 1
+            for v in shape:
+                numel *= v
+            g = torch.Generator().manual_seed(numel + len(topo))
+            X = torch.randn(ws, numel, generator=g, dtype=torch.float64)
+            t = X[r].float().view(shape).to(dev)
+            assert StagedFusedExchange.usable(None, t)
+            fn(t)
+            want = (M @ X)[r].view(shape).to(dev)
+            assert float((t.double() - want).abs().max()) < 1e-5, (topo, kind, shape)
+    assert L.launch_count() > launched0, "compat exchange did not launch our kernels"
 
     # broadcast
     sp = ExchangeSpec("allreduce", "allreduce", "equal", 0.5, None, ws)

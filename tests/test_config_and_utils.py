@@ -187,3 +187,47 @@ def test_dtype_flag_selects_the_engine():
             make_engine(Config(dtype="fp32", engine="native"), fake_gpu)
     finally:
         del os.environ["LDNN_TINY_WIDTHS"]
+
+
+def test_launcher_env_understands_mpirun_and_srun():
+    """`mpirun -n N python main.py` (how upstream starts the ring variants) must not start N one-rank jobs."""
+    from ldnn_b200.launch import launcher_env
+    assert launcher_env({}) == (0, 1, 0)
+    assert launcher_env({"RANK": "3", "WORLD_SIZE": "8", "LOCAL_RANK": "3"}) == (3, 8, 3)
+    assert launcher_env({"OMPI_COMM_WORLD_RANK": "2", "OMPI_COMM_WORLD_SIZE": "4", "OMPI_COMM_WORLD_LOCAL_RANK": "0"}) == (2, 4, 0)
+    assert launcher_env({"PMI_RANK": "1", "PMI_SIZE": "2"}) == (1, 2, 1)
+    assert launcher_env({"SLURM_PROCID": "5", "SLURM_NTASKS": "16", "SLURM_LOCALID": "1"}) == (5, 16, 1)
+    # torchrun's variables win when several launch systems are visible (srun -> torchrun)
+    assert launcher_env({"RANK": "1", "WORLD_SIZE": "2", "SLURM_PROCID": "0", "SLURM_NTASKS": "1"}) == (1, 2, 1)
+
+
+def test_checkpoint_keeps_every_ranks_own_replica(tmp_path):
+    """Replicas diverge under the reference's schedule; a resume must not collapse them onto rank 0."""
+    import warnings
+    from ldnn_b200.engine import OptimConfig, TorchEngine
+    from ldnn_b200.utils.checkpoint import load_checkpoint, rank_path, save_checkpoint, save_rank_state
+    from test_flat_optimizer import tiny_spec
+    engs = [TorchEngine(tiny_spec(), "cpu", OptimConfig()) for _ in range(2)]
+    for r, e in enumerate(engs):
+        e.flat.params.add_(0.1 * (r + 1))
+        e.flat.m.fill_(float(r + 1))
+        e.flat.step = 7
+    path = str(tmp_path / "c.pt")
+    save_checkpoint(path, engs[0], epoch=4)
+    save_rank_state(path, engs[1], rank=1, world_size=2, epoch=4)
+    assert rank_path(path, 0) == path and rank_path(path, 1) == path + ".rank1"
+    for r in range(2):
+        fresh = TorchEngine(tiny_spec(), "cpu", OptimConfig())
+        assert load_checkpoint(path, fresh, rank=r, world_size=2) == 4
+        for sl in fresh.flat.slots:           # per tensor: the alignment padding between tensors is not state
+            assert torch.equal(fresh.flat.view(fresh.flat.params, sl.key), engs[r].flat.view(engs[r].flat.params, sl.key))
+            assert torch.equal(fresh.flat.view(fresh.flat.m, sl.key), engs[r].flat.view(engs[r].flat.m, sl.key))
+    # a side file from another epoch is not trusted: rank 0's state, with a warning
+    save_rank_state(path, engs[1], rank=1, world_size=2, epoch=3)
+    fresh = TorchEngine(tiny_spec(), "cpu", OptimConfig())
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        load_checkpoint(path, fresh, rank=1, world_size=2)
+    k0 = fresh.flat.slots[0].key
+    assert torch.equal(fresh.flat.view(fresh.flat.params, k0), engs[0].flat.view(engs[0].flat.params, k0))
+    assert any("replica" in str(x.message) for x in w)

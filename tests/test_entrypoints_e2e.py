@@ -51,3 +51,25 @@ def test_step_sync_shard_weighted_and_resume(tmp_path):
     # resume: one more global epoch
     launch("Disbalanced Ring", 2, ["--sync", "step", "--aggregation_type", "shard", "--shard_ratios", "3", "1",
                                     "--resume", str(ck), "--epochs_global", "3"], out)
+
+
+def test_time_limit_cuts_the_straggler_short(tmp_path):
+    """--time_limit as intended upstream (trainer.py:112-119,134-139; unreachable there): with shards 6:1 the small
+    rank finishes every local epoch first and announces it; the big rank stops `time_limit` seconds later instead of
+    finishing its shard, and nobody deadlocks (the epoch's collective sits after the loop)."""
+    import json
+    out = tmp_path / "G"
+    args = ["--shard_ratios", "6", "1", "--aggregation_type", "shard", "--synthetic_train", "448", "--batch_size", "8",
+            "--epochs_local", "2"]
+    launch("Disbalanced All-Reduce", 2, args + ["--time_limit", "0"], out)
+    m = json.loads((out / "metrics.json").read_text())
+    assert len(m["straggler_cuts"]) == 4 and all(c == [0] for c in m["straggler_cuts"]), m["straggler_cuts"]
+    full = 448 * 0.8 * 6 / 7 / 8                        # steps of rank 0's whole shard
+    done = [len(v) for v in m["all_epochs_losses"]]     # pooled per local epoch: rank 0's steps + rank 1's
+    assert all(d < 0.8 * (full + full / 6) for d in done), (done, full)
+    # with a generous limit nobody is cut and every step of both shards runs
+    out2 = tmp_path / "G2"
+    launch("Disbalanced All-Reduce", 2, args + ["--time_limit", "600"], out2)
+    m2 = json.loads((out2 / "metrics.json").read_text())
+    assert all(c == [] for c in m2["straggler_cuts"])
+    assert sum(len(v) for v in m2["all_epochs_losses"]) > sum(done)

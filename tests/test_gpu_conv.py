@@ -154,8 +154,6 @@ def test_cluster_multicast_weights(case, splits, dt):
     assert _run(case, K.DGRAD, dt, cluster=2, block_n=128, splits=splits) < _tol(dt)[0]
 
 
-@pytest.mark.skipif(not os.environ.get("LDNN_TEST_PAIR"), reason="staged cta_group::2 variant: not yet run on hardware "
-                    "(set LDNN_TEST_PAIR=1, and run it under `timeout`)")
 @pytest.mark.parametrize("case", [(64, 16, 16, 128, 128, 3, 1, 1), (64, 8, 8, 256, 256, 3, 1, 1),
                                   (64, 16, 16, 128, 256, 3, 2, 1), (8, 14, 14, 256, 256, 3, 1, 1)])
 @pytest.mark.parametrize("block_n", [128, 256])

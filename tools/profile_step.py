@@ -8,7 +8,8 @@ from ldnn_b200.engine import OptimConfig
 from ldnn_b200.models import enhanced_cnn_spec
 from ldnn_b200.models.native import NativeEngine
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
-eng = NativeEngine(enhanced_cnn_spec(), "cuda:0", OptimConfig(), batch_size=64)
+dtype = sys.argv[2] if len(sys.argv) > 2 else "tf32"
+eng = NativeEngine(enhanced_cnn_spec(), "cuda:0", OptimConfig(), batch_size=64, dtype=dtype)
 x = torch.randn(64, 3, 32, 32, device="cuda"); y = torch.randint(0, 10, (64,), device="cuda")
 for _ in range(steps):
     loss, _ = eng.train_step(x, y)
