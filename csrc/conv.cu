@@ -78,6 +78,23 @@ static int make_map(CUtensorMap* m, const void* base, int rank, const uint64_t* 
   return LDNN_OK;
 }
 
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory
+// hung the GPU.  The cluster = 2 variant multicasts the weight tile, so every tensor it maps must be plain device memory
+// of the current device: not a peer mapping, not an IPC import, not host memory.
+static int require_local_device_memory(const void* ptr, const char* what) {
+  if (ptr == nullptr) return LDNN_OK;
+  int cur = -1;
+  LDNN_CUDA(cudaGetDevice(&cur));
+  cudaPointerAttributes at;
+  cudaError_t e = cudaPointerGetAttributes(&at, ptr);
+  if (e != cudaSuccess) { cudaGetLastError(); at.type = cudaMemoryTypeUnregistered; at.device = -1; }
+  LDNN_ARG(at.type == cudaMemoryTypeDevice && at.device == cur,
+           "conv cluster=2 (TMA multicast of the weight tile) needs %s in this GPU's own device memory "
+           "(pointer %p: memory type %d on device %d, current device %d); use cluster=0 or cluster=-2", what, ptr,
+           (int)at.type, at.device, cur);
+  return LDNN_OK;
+}
+
 static int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 static int cdiv(int a, int b) { return (a + b - 1) / b; }
 static int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
@@ -158,6 +175,12 @@ static int build(const ldnn_conv_desc& d, Plan& plan, bool dry) {
   plan.lite = d.lite ? 1 : 0;
   plan.cluster = ((d.cluster == 2 || d.cluster == -2) && d.mode != MODE_WGRAD && bn_ >= 128) ? 2 : 1;
   plan.pair = (d.cluster == -2 && plan.cluster == 2) ? 1 : 0;
+  if (plan.cluster == 2 && !plan.pair && !dry) {
+    int rc = require_local_device_memory(d.x, "x");
+    if (!rc) rc = require_local_device_memory(d.w, "w");
+    if (!rc) rc = require_local_device_memory(d.y, "y");
+    if (rc) return rc;
+  }
   LDNN_ARG(!(plan.pair && d.lite), "the CTA-pair variant has no lite form");
   plan.out = (d.mode == MODE_FPROP) ? d.y : (d.mode == MODE_DGRAD ? const_cast<void*>(d.x) : d.dw);
   plan.addend = d.addend ? d.addend : plan.out;

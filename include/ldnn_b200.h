@@ -39,7 +39,10 @@ typedef struct {
   unsigned int* tickets; /* split-K arrival counters, zero-initialised once                */
   unsigned int a_lbo, a_sbo, b_lbo, b_sbo; /* debug: override smem-descriptor strides (0 = default) */
   int cluster;         /* fprop/dgrad: 2 = thread-block clusters of two M tiles, weight tile TMA-multicast to both
-                          (needs block_n >= 128 and an even number of M tiles); 0/1 = no cluster          */
+                          (needs block_n >= 128 and an even number of M tiles); x, w and y must then be this GPU's own
+                          device memory (checked): TMA multicast loads here read only this GPU's memory, since on B200
+                          a TMA multicast load from another GPU's memory hung the GPU.  -2 = CTA pair running one
+                          tcgen05.mma.cta_group::2 (no multicast load).  0/1 = no cluster                        */
   int lite;            /* 1 = short pipeline (~96 KB smem) + 4 epilogue warps so two CTAs share an SM: for large
                           grids of short-K tiles (one CTA's prologue/epilogue hides under the other's mainloop) */
   int atomic_out;      /* wgrad: split-K partial tiles are red.add'ed straight into dw (caller zeroes dw

@@ -177,16 +177,20 @@ V_FULL, V_LITE, V_MCAST, V_PAIR = 0, 1, 2, 3
 
 
 def variant_kwargs(variant) -> dict:
-    """ConvPlan keyword arguments of a tuned variant: 0 full pipeline, 1 lite (two CTAs per SM), 2 clusters of two
-    M tiles with the weight tile TMA-multicast, 3 CTA pairs running one tcgen05.mma.cta_group::2 (UMMA_M = 256)."""
+    """ConvPlan keyword arguments of a tuned variant: 0 full pipeline, 1 lite (two CTAs per SM), 3 CTA pairs running
+    one tcgen05.mma.cta_group::2 (UMMA_M = 256).  Variant 2 (clusters of two M tiles with the weight tile
+    TMA-multicast) is NOT selectable here: the engines keep their weights in symmetric memory that peers map, and TMA
+    multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung
+    the GPU — so the engines never issue one; a stored 2 runs as the full pipeline.  The kernel variant itself stays
+    available to direct callers (`ConvPlan(cluster=2)`) on plain local tensors, which the library checks."""
     v = int(variant)
-    return {"lite": v == V_LITE, "cluster": {V_MCAST: 2, V_PAIR: -2}.get(v, 1)}
+    return {"lite": v == V_LITE, "cluster": -2 if v == V_PAIR else 1}
 
 
 def tuned_conv_config(mode, geo, make_plan, enabled=True, dtype=0):
     """Returns (block_n, splits, variant) — (0, 0, 0) = library heuristics.  `make_plan(block_n, splits, variant)`
     must build a runnable plan (private scratch) for timing; see `variant_kwargs`.  `lite` is tried only for
-    grids of more than one wave, the cluster / pair forms for 128- and 256-wide tiles of fprop and dgrad.
+    grids of more than one wave, the CTA-pair form for 128- and 256-wide tiles of fprop and dgrad.
     `dtype`: 0 bf16, 1 tf32 (separate tunings)."""
     global _TUNE_FILE_LOADED
     key = (int(dtype), int(mode)) + tuple(int(v) for v in geo)
@@ -205,10 +209,10 @@ def tuned_conv_config(mode, geo, make_plan, enabled=True, dtype=0):
     best_cfg, best_t = (0, 0, V_FULL), _time_plan(base)
     seen = {(0, base.grid, V_FULL)}
     cands = [(0, 0)] + conv_candidates(mode, geo, n_total)
-    variants = (V_FULL, V_LITE) if mode == WGRAD else (V_FULL, V_LITE, V_PAIR, V_MCAST)
+    variants = (V_FULL, V_LITE) if mode == WGRAD else (V_FULL, V_LITE, V_PAIR)
     for bn, sp in cands:
         for var in variants:
-            if var in (V_PAIR, V_MCAST) and bn < 128:
+            if var == V_PAIR and bn < 128:
                 continue
             try:
                 plan = make_plan(bn, sp, var)
