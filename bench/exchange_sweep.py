@@ -68,6 +68,8 @@ def main():
     ap.add_argument("--blocks", type=int, default=64)   # the sweep has the GPU to itself: 64 CTAs for every kernel
     ap.add_argument("--modes", default="reduce,update")
     ap.add_argument("--out", default="gpurun_out/exchange_sweep.json")
+    ap.add_argument("--nvlink_at_mb", type=int, default=128,
+                    help="at this payload also read the driver's NVLink byte counters around 10 calls (0 = off)")
     a = ap.parse_args()
     from ldnn_b200.engine import OptimConfig
     from ldnn_b200.launch import init_runtime, shutdown
@@ -85,7 +87,8 @@ def main():
     opt = OptimConfig(kind="adam", lr=1e-3)
     rows = []
     sizes = [1 << k for k in range(10, 31) if (1 << k) <= a.max_mb << 20]
-    impls = ["allreduce", "ring", "double_ring", "nccl"]
+    # "allreduce" = the two-shot P2P kernel; "allreduce_nvls" = the in-switch kernel on the same (multicast-capable) slabs
+    impls = ["allreduce", "allreduce_nvls", "ring", "double_ring", "nccl"]
     clk = ClockSampler(dev.index or 0, period_s=0.1)
     clk.__enter__()
     nvls_seen = False
@@ -93,8 +96,15 @@ def main():
         for topo in impls:
             ex = None
             if topo != "nccl":
-                ex = FusedExchanger(ExchangeSpec(topo, "allreduce", "equal", 0.5, None, ws), rt, eng, comm_blocks=a.blocks)
-                nvls_seen = nvls_seen or bool(getattr(ex, "nvls", False))
+                ex = FusedExchanger(ExchangeSpec(topo.replace("_nvls", ""), "allreduce", "equal", 0.5, None, ws), rt, eng,
+                                    comm_blocks=a.blocks)
+                if topo == "allreduce":
+                    ex.nvls = False                   # two-shot kernel (peer loads / stores), whatever the slabs allow
+                elif topo == "allreduce_nvls":
+                    if not ex.nvls:                   # no multicast mapping on this host: no such column
+                        ex.close()
+                        continue
+                    nvls_seen = True
             for nbytes in sizes:
                 n = max(nbytes // 4, 4 * ws)
                 if ex is not None:
@@ -135,7 +145,8 @@ def main():
                 rows.append({"mode": mode, "impl": topo, "bytes": nb, "us": ms * 1e3, "algbw_GBs": nb / ms / 1e6,
                              "busbw_GBs": bus, "link_frac": bus / LINK_GBS if ws > 1 else None,
                              "roofline_frac": max(t_link, t_hbm) / (ms / 1e3), "world": ws,
-                             "nvls": bool(ex is not None and getattr(ex, "nvls", False) and topo == "allreduce")})
+                             "nvls": topo == "allreduce_nvls",
+                             "nvlink": nvlink_probe(one, nb, dev, rt) if (a.nvlink_at_mb and nb == a.nvlink_at_mb << 20) else None})
                 buf.normal_()
             if ex is not None:
                 ex.check(); ex.close()
@@ -153,10 +164,54 @@ def main():
             for nb in sorted({r["bytes"] for r in rows}):
                 cells = []
                 for t in impls:
-                    r = [x for x in rows if x["impl"] == t and x["bytes"] == nb and x["mode"] == mode][0]
+                    rr = [x for x in rows if x["impl"] == t and x["bytes"] == nb and x["mode"] == mode]
+                    if not rr:
+                        cells.append("-")
+                        continue
+                    r = rr[0]
                     cells.append(f"{r['busbw_GBs']:7.1f}|{r['us']:6.0f}|{r['roofline_frac']:5.2f}")
                 print(f"{nb:>12} " + " ".join(f"{c:>22}" for c in cells))
+        probes = [r for r in rows if r.get("nvlink")]
+        if probes:
+            print("## NVLink traffic of rank 0's GPU (nvidia-smi nvlink -gt d, all links), per call, vs the algorithmic "
+                  "2(W-1)/W x payload each way")
+            for r in probes:
+                v = r["nvlink"]
+                if "error" in v:
+                    print(f"{r['mode']:>7} {r['impl']:>15}: counters unavailable ({v['error']})")
+                    continue
+                print(f"{r['mode']:>7} {r['impl']:>15} {r['bytes']:>11} B: tx {v['tx_MB_per_call']:8.1f} MB  rx "
+                      f"{v['rx_MB_per_call']:8.1f} MB  algorithmic {v['algorithmic_MB_each_way']:8.1f} MB")
     shutdown(rt)
+
+
+def _nvlink_kib(idx):
+    """(tx KiB, rx KiB) summed over the links of GPU `idx`, from the driver's NVLink data counters."""
+    import re
+    import subprocess
+    out = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(idx)], capture_output=True, text=True,
+                         timeout=20).stdout
+    tx = sum(int(v) for v in re.findall(r"Data Tx:\s*(\d+)\s*KiB", out))
+    rx = sum(int(v) for v in re.findall(r"Data Rx:\s*(\d+)\s*KiB", out))
+    return tx, rx
+
+
+def nvlink_probe(one, nbytes, dev, rt, calls=10):
+    """Bytes that crossed rank 0's NVLink ports during `calls` exchanges (collective: every rank runs them)."""
+    try:
+        dist.barrier(); torch.cuda.synchronize()
+        before = _nvlink_kib(dev.index or 0) if rt.rank == 0 else (0, 0)
+        dist.barrier()
+        for _ in range(calls):
+            one()
+        torch.cuda.synchronize(); dist.barrier()
+        after = _nvlink_kib(dev.index or 0) if rt.rank == 0 else (0, 0)
+        ws = rt.world_size
+        return {"tx_MB_per_call": (after[0] - before[0]) * 1024 / calls / 1e6,
+                "rx_MB_per_call": (after[1] - before[1]) * 1024 / calls / 1e6,
+                "algorithmic_MB_each_way": 2 * (ws - 1) / ws * nbytes / 1e6, "calls": calls}
+    except Exception as e:     # counters not exposed on this host
+        return {"error": f"{type(e).__name__}: {e}"[:200]}
 
 
 if __name__ == "__main__":
