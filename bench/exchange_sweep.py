@@ -68,8 +68,9 @@ def main():
     ap.add_argument("--blocks", type=int, default=64)   # the sweep has the GPU to itself: 64 CTAs for every kernel
     ap.add_argument("--modes", default="reduce,update")
     ap.add_argument("--out", default="gpurun_out/exchange_sweep.json")
-    ap.add_argument("--nvlink_at_mb", type=int, default=128,
-                    help="at this payload also read the driver's NVLink byte counters around 10 calls (0 = off)")
+    ap.add_argument("--nvlink_at_mb", type=int, default=0,
+                    help="at this payload also read the driver's NVLink byte counters around 10 calls (0 = off; on the "
+                         "B200 pool used here `nvidia-smi nvlink -gt d` reads 0 KiB on every link, so it is off)")
     a = ap.parse_args()
     from ldnn_b200.engine import OptimConfig
     from ldnn_b200.launch import init_runtime, shutdown
@@ -101,6 +102,7 @@ def main():
                 if topo == "allreduce":
                     ex.nvls = False                   # two-shot kernel (peer loads / stores), whatever the slabs allow
                 elif topo == "allreduce_nvls":
+                    ex.nvls = bool(getattr(ex, "nvls_capable", ex.nvls))   # measure it whatever the size policy says
                     if not ex.nvls:                   # no multicast mapping on this host: no such column
                         ex.close()
                         continue

@@ -711,11 +711,14 @@ extern "C" int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int n
   const long long n4 = x->n / 4;
   const long long chunk4 = (n4 / num_rings + c->world) / c->world + 1;
   // sub-chunks: one per hand-off chain.  Every group of 128 threads runs its own chains (4 groups per CTA).  Under load
-  // a hand-off (system-scope release + flag + the consumer's poll) costs ~13 us, during which the chain is idle: a group
-  // therefore owns ~8 chains per step, so that it always has another sub-chunk to stream while hand-offs are in flight.
-  // Never shorter than 4 KB (2 x 16 B per thread); the flag table (one word per chain) caps J.
+  // a hand-off (system-scope release, which waits for the group's remote stores to be acknowledged, + flag + the
+  // consumer's poll) costs ~10-13 us and is serial within a group, so the payload is cut into as FEW chains as keep all
+  // groups busy: `chains` per group and step (default 1; LDNN_RING_CHAINS), never shorter than 16 KB.  Measured on
+  // 8 x B200 at 128 MB: 8 chains of 8 KB per group 158 GB/s, 2 of 32 KB 484 GB/s (hand-off bound in both).
+  static int chains = 0;
+  if (chains == 0) { const char* e = getenv("LDNN_RING_CHAINS"); chains = e ? std::max(1, atoi(e)) : 1; }
   const int gpr = std::max(1, c->blocks * kGroups / num_rings);
-  long long sub4 = std::max<long long>(256, (chunk4 + 8 * gpr - 1) / (8 * gpr));
+  long long sub4 = std::max<long long>(1024, (chunk4 + (long long)chains * gpr - 1) / ((long long)chains * gpr));
   int J = (int)((chunk4 + sub4 - 1) / sub4);
   const int maxJ = kFlagWords / 2;
   if (J > maxJ) { J = maxJ; sub4 = (chunk4 + J - 1) / J; }

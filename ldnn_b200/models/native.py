@@ -359,7 +359,14 @@ class _StepPlan:
         need = 0
         for m, g in descs:
             need = max(need, K.conv_query(m, *g, atomic_out=(atomic and m == K.WGRAD), dtype=eng.dcode)[0])
-            if eng.autotune:                        # the tuner may pick any candidate: size for the largest
+            if n != eng.max_batch:                   # this size replays the nominal batch's tuning (see _tuned)
+                cfg = K.tuned_conv_config(m, (eng.max_batch,) + tuple(g[1:]), None, False, eng.dcode)
+                try:
+                    need = max(need, K.conv_query(m, *g, block_n=cfg[0], splits=cfg[1],
+                                                  atomic_out=(atomic and m == K.WGRAD), dtype=eng.dcode)[0])
+                except L.LdnnError:
+                    pass
+            if eng.autotune and n == eng.max_batch:  # the tuner may pick any candidate: size for the largest
                 n_total = g[4] if m == K.FPROP else g[3]
                 for bn, sp in K.conv_candidates(m, g, n_total):
                     try:
@@ -469,6 +476,25 @@ class _StepPlan:
             self.ops.insert(zero_slot, (view.zero_, False))
             self.bucket_marks = [(k + 1, lo, hi) for k, lo, hi in self.bucket_marks]
 
+    def _tuned(self, mode, geo, make_plan, allow=True):
+        """(block_n, splits, variant) for one conv of this plan.  Only the engine's nominal batch size is tuned by
+        timing (and served from the shipped tunings): a training run meets a new partial-batch size after almost
+        every re-shard, and timing ~70 candidate plans per layer for each of them cost seconds per global epoch
+        (the `Balanced Ring` entrypoint fell from 83 k to 35 k samples/s that way in round 1).  Other batch sizes
+        reuse the nominal size's choice when it builds for them, else the library heuristics."""
+        eng = self.eng
+        if self.n == eng.max_batch or os.environ.get("LDNN_TUNE_ALL_BATCHES"):
+            return K.tuned_conv_config(mode, geo, make_plan, eng.autotune and allow, eng.dcode)
+        nominal = (eng.max_batch,) + tuple(geo[1:])
+        cfg = K.tuned_conv_config(mode, nominal, None, False, eng.dcode)
+        if cfg != (0, 0, 0):
+            try:
+                make_plan(*cfg)
+                return cfg
+            except L.LdnnError:
+                pass
+        return (0, 0, 0)
+
     def _fwd_unit(self, u: ConvBN, W, P):
         eng, n = self.eng, self.n
         ci = eng.info[u.conv_key]
@@ -493,9 +519,9 @@ class _StepPlan:
             geo, xin = (n, ci.P, ci.Q, ci.kdim, u.cout, 1, 1, 0), self.col[u.conv_key]
         else:
             geo, xin = (n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad), self.act[u.src]
-        bn_, sp_, lt_ = K.tuned_conv_config(
+        bn_, sp_, lt_ = self._tuned(
             K.FPROP, geo, lambda b, s_, l_: K.ConvPlan(K.FPROP, *geo, xin, w, yraw, bn_sums=fsum, block_n=b, splits=s_,
-                                                       **K.variant_kwargs(l_)), eng.autotune, eng.dcode)
+                                                       **K.variant_kwargs(l_)))
         plan = K.ConvPlan(K.FPROP, *geo, xin, w, yraw, workspace=self.ws, bn_sums=fsum, block_n=bn_, splits=sp_,
                           **K.variant_kwargs(lt_))
         self._add(plan.run, plan.num_launches)
@@ -548,11 +574,9 @@ class _StepPlan:
             geo = (n, ci.H, ci.W, u.cin, u.cout, u.k, u.stride, u.pad)
             xin = self.act[u.src]
         atomic = not eng.deterministic
-        bn_, sp_, lt_ = K.tuned_conv_config(
+        bn_, sp_, lt_ = self._tuned(
             K.WGRAD, geo, lambda b, s_, l_: K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, atomic_out=atomic,
-                                                       block_n=b, splits=s_, **K.variant_kwargs(l_)),
-            eng.autotune and atomic,
-            eng.dcode)
+                                                       block_n=b, splits=s_, **K.variant_kwargs(l_)), allow=atomic)
         wg = K.ConvPlan(K.WGRAD, *geo, xin, None, dyr, dw=gw, workspace=self.ws, atomic_out=atomic, block_n=bn_,
                         splits=sp_, **K.variant_kwargs(lt_))
         if atomic and K.conv_query(K.WGRAD, *geo, block_n=bn_, splits=sp_, dtype=eng.dcode)[0] > 0:   # split-K → red.add into a zeroed slice
@@ -568,9 +592,9 @@ class _StepPlan:
         if not acc and not full_cover:
             self._add(lambda: dx.zero_(), 0)
             acc = True
-        bn_, sp_, lt_ = K.tuned_conv_config(
+        bn_, sp_, lt_ = self._tuned(
             K.DGRAD, geo, lambda b, s_, l_: K.ConvPlan(K.DGRAD, *geo, dx, w, dyr, addend=dx, accumulate=True, block_n=b,
-                                                       splits=s_, **K.variant_kwargs(l_)), eng.autotune, eng.dcode)
+                                                       splits=s_, **K.variant_kwargs(l_)))
         fuse = None
         if u.conv_key in self.fuse_into:
             ow = self.fuse_into[u.conv_key]

@@ -126,7 +126,13 @@ class FusedExchanger:
             tens = engine.symm_tensor(name) if (h is None and hasattr(engine, "symm_tensor")) else None
             self._bufs[name] = SymmetricBuffer(name, p, h, nb, rt, tensor=tens)
         # in-switch reduce (multimem) is used when both slabs have a multicast mapping (LDNN_NVLS=1 + NVSwitch)
-        self.nvls = all(self._bufs[k].multicast for k in ("params", "grads"))
+        # The switch-side reduce moves ~S bytes per GPU and direction instead of 2S(W-1)/W: a win that grows with W
+        # (8 GPUs: 827 vs 640 GB/s bus bandwidth at 512 MB) and a loss at W = 2, where both move S and the multimem
+        # round trip is slower than peer loads (360 vs 600 GB/s): used from LDNN_NVLS_MIN_WORLD ranks up (default 4);
+        # LDNN_NVLS=1 forces it at any size.
+        self.nvls_capable = all(self._bufs[k].multicast for k in ("params", "grads"))
+        self.nvls = self.nvls_capable and (os.environ.get("LDNN_NVLS") == "1" or
+                                           self.world >= int(os.environ.get("LDNN_NVLS_MIN_WORLD", "4")))
         t, h, p = K.symm_alloc(L.SIGNAL_WORDS * 4, dev)
         self._signal_t = t
         self._bufs["signal"] = SymmetricBuffer("signal", p, h, L.SIGNAL_WORDS * 4, rt)
