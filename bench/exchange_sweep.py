@@ -68,6 +68,8 @@ def main():
     ap.add_argument("--blocks", type=int, default=64)   # the sweep has the GPU to itself: 64 CTAs for every kernel
     ap.add_argument("--modes", default="reduce,update")
     ap.add_argument("--out", default="gpurun_out/exchange_sweep.json")
+    ap.add_argument("--impls", default="allreduce,allreduce_nvls,ring,double_ring,nccl")
+    ap.add_argument("--min_kb", type=int, default=1)
     ap.add_argument("--nvlink_at_mb", type=int, default=0,
                     help="at this payload also read the driver's NVLink byte counters around 10 calls (0 = off; on the "
                          "B200 pool used here `nvidia-smi nvlink -gt d` reads 0 KiB on every link, so it is off)")
@@ -87,9 +89,9 @@ def main():
     eng.flat.params.normal_()
     opt = OptimConfig(kind="adam", lr=1e-3)
     rows = []
-    sizes = [1 << k for k in range(10, 31) if (1 << k) <= a.max_mb << 20]
+    sizes = [1 << k for k in range(10, 31) if (a.min_kb << 10) <= (1 << k) <= a.max_mb << 20]
     # "allreduce" = the two-shot P2P kernel; "allreduce_nvls" = the in-switch kernel on the same (multicast-capable) slabs
-    impls = ["allreduce", "allreduce_nvls", "ring", "double_ring", "nccl"]
+    impls = [t for t in a.impls.split(",") if t]
     clk = ClockSampler(dev.index or 0, period_s=0.1)
     clk.__enter__()
     nvls_seen = False

@@ -713,8 +713,9 @@ extern "C" int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int n
   // sub-chunks: one per hand-off chain.  Every group of 128 threads runs its own chains (4 groups per CTA).  Under load
   // a hand-off (system-scope release, which waits for the group's remote stores to be acknowledged, + flag + the
   // consumer's poll) costs ~10-13 us and is serial within a group, so the payload is cut into as FEW chains as keep all
-  // groups busy: `chains` per group and step (default 1; LDNN_RING_CHAINS), never shorter than 16 KB.  Measured on
-  // 8 x B200 at 128 MB: 8 chains of 8 KB per group 158 GB/s, 2 of 32 KB 484 GB/s (hand-off bound in both).
+  // groups busy: `chains` per group and step (default 1; LDNN_RING_CHAINS), never shorter than 16 KB.  Measured at
+  // 128 MB: 8 x B200, 8 chains of 8 KB per group 158 GB/s, 2 of 32 KB 484 GB/s; 4 x B200, 4 / 2 / 1 chains per group
+  // 458 / 476 / 500 GB/s (profiles/ring_chains_4gpu.txt) — hand-off bound in every case, so fewer is better.
   static int chains = 0;
   if (chains == 0) { const char* e = getenv("LDNN_RING_CHAINS"); chains = e ? std::max(1, atoi(e)) : 1; }
   const int gpr = std::max(1, c->blocks * kGroups / num_rings);
