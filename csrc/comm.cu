@@ -443,7 +443,12 @@ __device__ __forceinline__ bool poll_slot(const Ctx& x, const float4* p, float4&
   v = ld_sys_f4(p);
   if (!(is_sentinel(v.x) | is_sentinel(v.y) | is_sentinel(v.z) | is_sentinel(v.w))) return true;
   const long long t0 = clock64();
+  unsigned int ns = 32;
   for (;;) {
+    // back off while waiting: a rank that is ahead of its upstream peer (uneven shards, skewed arrival) would otherwise
+    // have tens of thousands of threads hammering L2 with probes next to its own backward kernels
+    __nanosleep(ns);
+    if (ns < 512) ns <<= 1;
     v = ld_sys_f4(p);
     if (!(is_sentinel(v.x) | is_sentinel(v.y) | is_sentinel(v.z) | is_sentinel(v.w))) return true;
     if ((unsigned long long)(clock64() - t0) > x.timeout) {

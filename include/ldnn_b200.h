@@ -93,7 +93,9 @@ int ldnn_bn_fwd_stats(const void* y, int M, int C, int chunks, float* partial, u
  * device current): make that first call before any stream capture begins.  Every call on a device
  * shares the one array, and the array keeps the previous call's contents (the ticket is cleared in
  * stream order at the start of each call): two calls that overlap on the GPU race with each other —
- * keep them on one stream or order them yourself.
+ * keep them on one stream or order them yourself.  The per-device address cache inside the library is written
+ * without a lock: two host threads making the FIRST call on a device at the same moment both look the address up and
+ * store the same value, which is harmless.
  * This entry point has no counterpart in the reference. */
 int ldnn_bn_fwd_stats_noalloc(const void* y, int M, int C, int chunks, const float* gamma, const float* beta,
                               float* running_mean, float* running_var, long long* num_batches_tracked,

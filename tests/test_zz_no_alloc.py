@@ -74,3 +74,27 @@ def test_noalloc_refuses_requests_beyond_its_scratch():
     assert "exceeds the built-in scratch" in lib.ldnn_last_error().decode()
     torch.cuda.synchronize()
     assert int(o["nbt"]) == 0                # nothing was launched
+
+
+def test_noalloc_on_a_side_stream():
+    """The ticket is cleared and the kernel launched in the order of the stream the caller passes: two calls queued on
+    one non-default stream, with the results read only after that stream has drained."""
+    from ldnn_b200.ops import _lib as L
+    lib = L.lib()
+    M, C_, chunks = 4096, 256, 32
+    g = torch.Generator().manual_seed(5)
+    gamma, beta = (torch.rand(C_, generator=g) + 0.5).cuda(), torch.randn(C_, generator=g).cuda()
+    ys = [(torch.randn(M, C_, generator=g) * (1 + i)).cuda().bfloat16() for i in range(2)]
+    o = _outputs(C_)
+    torch.cuda.synchronize()
+    st = torch.cuda.Stream()
+    for y in ys:
+        rc = lib.ldnn_bn_fwd_stats_noalloc(_vp(y), M, C_, chunks, _vp(gamma), _vp(beta), _vp(o["rm"]), _vp(o["rv"]),
+                                           _vp(o["nbt"]), _vp(o["sm"]), _vp(o["si"]), _vp(o["sc"]), _vp(o["sh"]),
+                                           C.c_float(EPS), C.c_float(MOM), C.c_void_p(st.cuda_stream))
+        assert rc == 0, lib.ldnn_last_error().decode()
+    st.synchronize()
+    yf = ys[1].float()
+    assert int(o["nbt"]) == 2
+    assert torch.allclose(o["sm"], yf.mean(0), atol=1e-3, rtol=1e-3)
+    assert torch.allclose(o["si"], (yf.var(0, unbiased=False) + EPS).rsqrt(), atol=1e-3, rtol=1e-3)

@@ -1,9 +1,9 @@
 #!/bin/bash
-# usage: gpu_r2_mgpu.sh N [max_mb] [full] — multi-GPU evidence of round 2 on N GPUs: exchange kernels on real peers (bulk
+# usage: gpu_multi.sh N [max_mb] [full] — multi-GPU evidence of round 2 on N GPUs: exchange kernels on real peers (bulk
 # rings, flag-free rings, two-shot, NVLS, compat functions), exchange sweep with clock record + NVLink byte counters,
 # bench both arms (headline + extras), entrypoint bench; with `full`: ResNet-50 @224 double ring and Disbalanced runs.
 N=${1:-2}; MAXMB=${2:-256}; FULL=${3:-}
-mkdir -p gpurun_out; S=gpurun_out/r2_mgpu_${N}_summary.txt; rm -f $S
+mkdir -p gpurun_out; S=gpurun_out/multi_${N}_summary.txt; rm -f $S
 run() { timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $1 "${@:2}"; }
 LDNN_RING_LL_MAX_MB=0 LDNN_NVLS=0 run 29541 tests/mgpu_worker.py > gpurun_out/mgpu_worker_bulk_$N.log 2>&1; echo "mgpu worker (bulk rings, IPC slabs) exit $?" >> $S
 run 29542 tests/mgpu_worker.py > gpurun_out/mgpu_worker_default_$N.log 2>&1; echo "mgpu worker (defaults: flag-free rings, NVLS) exit $?" >> $S

@@ -1,7 +1,7 @@
 #!/bin/bash
 # 4 GPUs: exchange kernels on real peers, full sweep with clock record, ring chain-count comparison, bench both arms, R50.
 N=4
-mkdir -p gpurun_out; S=gpurun_out/r2_mgpu_${N}_summary.txt; rm -f $S
+mkdir -p gpurun_out; S=gpurun_out/multi_${N}_summary.txt; rm -f $S
 run() { timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $1 "${@:2}"; }
 run 29542 tests/mgpu_worker.py > gpurun_out/mgpu_worker_default_$N.log 2>&1; echo "mgpu worker (defaults) exit $?" >> $S
 run 29544 bench/exchange_sweep.py --max_mb 512 --out gpurun_out/exchange_sweep_$N.json > gpurun_out/exchange_sweep_${N}gpu.txt 2>&1; echo "sweep exit $?" >> $S
