@@ -253,7 +253,7 @@ def run_ours(a):
     from ldnn_b200.config import Config, resolve
     from ldnn_b200.engine import make_engine
     from ldnn_b200.launch import init_runtime, shutdown
-    from ldnn_b200.parallel import make_exchanger
+    from ldnn_b200.parallel import bring_up, make_exchanger
     from ldnn_b200.utils.timing import ClockSampler
 
     rank, world, local = env_world()
@@ -278,8 +278,9 @@ def run_ours(a):
             ex_.set_shard_weights([v / sum(ratios) for v in ratios])
         return ex_
 
-    engine = make_engine(cfg, rt)
-    ex = exchanger_for(cfg, engine)
+    engine, ex = bring_up(cfg, rt, make_engine)       # falls back to CUDA-IPC slabs if the NVLS bring-up fails
+    if a.aggregation_type == "shard":
+        ex.set_shard_weights([v / sum(ratios) for v in ratios])
     ex.broadcast_state(engine)
     data = _Data(dev, rank, engine.spec.in_hw, engine.spec.head().num_classes)
 

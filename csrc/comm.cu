@@ -707,28 +707,41 @@ extern "C" int ldnn_allreduce_nvls(const ldnn_comm* c, const ldnn_exchange* x, v
                      x->weight[0]);
 }
 
+// sub-chunks of the bulk ring: one per hand-off chain.  Every group of 128 threads runs its own chains (4 groups per
+// CTA).  Under load a hand-off (system-scope release, which waits for the group's remote stores to be acknowledged, +
+// flag + the consumer's poll) costs ~10-13 us and is serial within a group, so the payload is cut into as FEW chains as
+// keep all groups busy: `chains` per group and step (default 1; LDNN_RING_CHAINS), never shorter than 16 KB.  Measured
+// at 128 MB: 8 x B200, 8 chains of 8 KB per group 158 GB/s, 2 of 32 KB 484 GB/s; 4 x B200, 4 / 2 / 1 chains per group
+// 458 / 476 / 500 GB/s (profiles/ring_chains_4gpu.txt) — hand-off bound in every case, so fewer is better.
+// Host-only arithmetic (no GPU needed): J chains of sub4 float4 each cover one rank's chunk of one ring; the flag
+// table (one word per chain and ring) caps J.
+extern "C" int ldnn_ring_plan(long long n, int world, int num_rings, int blocks, int chains, int* J_out,
+                              long long* sub4_out) {
+  LDNN_ARG(n >= 0 && n % 4 == 0 && world >= 1 && (num_rings == 1 || num_rings == 2) && blocks >= 1 && chains >= 1,
+           "ring plan: n=%lld world=%d rings=%d blocks=%d chains=%d", n, world, num_rings, blocks, chains);
+  const long long n4 = n / 4;
+  const long long chunk4 = (n4 / num_rings + world) / world + 1;
+  const int gpr = std::max(1, blocks * kGroups / num_rings);
+  long long sub4 = std::max<long long>(1024, (chunk4 + (long long)chains * gpr - 1) / ((long long)chains * gpr));
+  int J = (int)((chunk4 + sub4 - 1) / sub4);
+  const int maxJ = kFlagWords / 2;
+  if (J > maxJ) { J = maxJ; sub4 = (chunk4 + J - 1) / J; }
+  if (J < 1) J = 1;
+  *J_out = J; *sub4_out = sub4;
+  return LDNN_OK;
+}
+
 extern "C" int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int num_rings, void* stream) {
   LDNN_ARG(x->n % 4 == 0, "ring: n %% 4");
   LDNN_ARG(num_rings == 1 || num_rings == 2, "ring: num_rings=%d", num_rings);
   LDNN_ARG(!(x->mode & LDNN_X_SELFMIX), "ring: self-weighted mixing is only available on the all-reduce schedule");
   LDNN_ARG(c->blocks >= num_rings, "ring: need >= %d blocks", num_rings);
   LDNN_ARG(c->world == 1 || x->recv[c->emulate ? 0 : c->rank] != nullptr, "ring: needs the symmetric `recv` staging slab");
-  const long long n4 = x->n / 4;
-  const long long chunk4 = (n4 / num_rings + c->world) / c->world + 1;
-  // sub-chunks: one per hand-off chain.  Every group of 128 threads runs its own chains (4 groups per CTA).  Under load
-  // a hand-off (system-scope release, which waits for the group's remote stores to be acknowledged, + flag + the
-  // consumer's poll) costs ~10-13 us and is serial within a group, so the payload is cut into as FEW chains as keep all
-  // groups busy: `chains` per group and step (default 1; LDNN_RING_CHAINS), never shorter than 16 KB.  Measured at
-  // 128 MB: 8 x B200, 8 chains of 8 KB per group 158 GB/s, 2 of 32 KB 484 GB/s; 4 x B200, 4 / 2 / 1 chains per group
-  // 458 / 476 / 500 GB/s (profiles/ring_chains_4gpu.txt) — hand-off bound in every case, so fewer is better.
   static int chains = 0;
   if (chains == 0) { const char* e = getenv("LDNN_RING_CHAINS"); chains = e ? std::max(1, atoi(e)) : 1; }
-  const int gpr = std::max(1, c->blocks * kGroups / num_rings);
-  long long sub4 = std::max<long long>(1024, (chunk4 + (long long)chains * gpr - 1) / ((long long)chains * gpr));
-  int J = (int)((chunk4 + sub4 - 1) / sub4);
-  const int maxJ = kFlagWords / 2;
-  if (J > maxJ) { J = maxJ; sub4 = (chunk4 + J - 1) / J; }
-  if (J < 1) J = 1;
+  int J = 1;
+  long long sub4 = 0;
+  ldnn_ring_plan(x->n, c->world, num_rings, c->blocks, chains, &J, &sub4);
   return launch_comm(ring_fused_kernel, *c, (cudaStream_t)stream, *c, *x, num_rings, J, sub4);
 }
 

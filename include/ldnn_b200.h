@@ -262,6 +262,8 @@ int ldnn_allreduce_fused(const ldnn_comm* c, const ldnn_exchange* x, void* strea
 int ldnn_allreduce_nvls(const ldnn_comm* c, const ldnn_exchange* x, void* mc_data, void* mc_params, void* stream);
 /* K-RING / K-DRING: reduce-scatter + all-gather around 1 or 2 (counter-rotating) rings */
 int ldnn_ring_fused(const ldnn_comm* c, const ldnn_exchange* x, int num_rings, void* stream);
+/* how ldnn_ring_fused cuts one rank's chunk into hand-off chains: J chains of sub4 float4 (host arithmetic only) */
+int ldnn_ring_plan(long long n, int world, int num_rings, int blocks, int chains, int* J, long long* sub4);
 /* K-RING / K-DRING for small and medium payloads: the same reduce-scatter + all-gather schedule with no flags, no
  * fences and no kernel-wide barrier — the payload travels through x->ll and announces itself (sentinel polling), one
  * dependency chain per element.  ldnn_ring_ll_slots = float4 slots one call uses per phase (pass it as the next call's

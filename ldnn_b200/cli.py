@@ -16,7 +16,7 @@ from . import data as D
 from .config import Config, parse_args
 from .engine import make_engine
 from .launch import init_runtime, shutdown
-from .parallel import make_exchanger
+from .parallel import bring_up
 from .trainer import TrainHistory, evaluate, refresh_shard_weights, train_global
 from .utils import checkpoint as ckpt
 from .utils import viz
@@ -43,11 +43,11 @@ def _run(cfg: Config, rt) -> TrainHistory:
 
 def _run_traced(cfg: Config, rt, phase) -> TrainHistory:
     with phase("bring-up"):
-        engine = make_engine(cfg, rt)
+        # engine + exchange together: the broadcast is the first thing that uses the exchange, and a failed NVLS
+        # bring-up falls back (collectively) to CUDA-IPC slabs
+        engine, exchanger = bring_up(cfg, rt, make_engine)
     bundle = D.get_data(cfg, rt.rank)
     D.place_bundle(bundle, cfg, rt)
-    # exchange bring-up first: the broadcast is the first thing that uses it
-    exchanger = make_exchanger(cfg, rt, engine, shard_weights=None)
     exchanger.broadcast_state(engine, src=0)
 
     shards = D.initial_shards(bundle, cfg, rt, engine)

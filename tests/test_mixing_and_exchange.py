@@ -69,3 +69,33 @@ def _exchange_worker(rank, ws):
 @pytest.mark.parametrize("ws", [2, 3])
 def test_dist_exchanger_matches_oracle(dist_runner, ws):
     dist_runner(_exchange_worker, ws)
+
+
+def test_ring_chain_plan_and_flag_free_pad_sizes():
+    """Host-side arithmetic of the ring kernels (native library, no GPU needed): the bulk ring's chains cover a rank's
+    chunk, respect the 16 KB floor and the flag table; the flag-free ring's slots per phase fit the pad the exchanger
+    allocates for its largest payload."""
+    import ctypes as C
+    from ldnn_b200.ops import _lib as L
+    lib = L.lib()
+    lib.ldnn_ring_plan.argtypes = [C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_longlong)]
+    for n in (4, 4 * 1000, 1 << 20, 44_595_904, 1 << 28):
+        for world in (1, 2, 3, 8):
+            for rings in (1, 2):
+                for blocks, chains in ((1, 1), (8, 1), (64, 1), (64, 2), (64, 8)):
+                    J, sub4 = C.c_int(0), C.c_longlong(0)
+                    assert lib.ldnn_ring_plan(n, world, rings, blocks, chains, C.byref(J), C.byref(sub4)) == 0
+                    chunk4 = -(-(n // 4 // rings + (1 if (n // 4) % rings else 0)) // world)      # ceil(ceil(n4/rings)/world)
+                    assert J.value >= 1 and J.value * sub4.value >= chunk4, (n, world, rings, blocks, chains)
+                    assert J.value <= (L.SIGNAL_WORDS - 4096 - 64) // 2
+                    assert sub4.value >= 1024 or J.value == (L.SIGNAL_WORDS - 4096 - 64) // 2
+                    groups = blocks * 4 // rings
+                    assert J.value <= max(1, chains * groups) + 1                               # ~`chains` per group
+    assert lib.ldnn_ring_plan(6, 2, 1, 8, 1, C.byref(J), C.byref(sub4)) != 0                     # n % 4
+    ll_max = 64 << 20
+    phase4 = 2 * (ll_max // 16) + 4096                                                           # FusedExchanger._ll_buf
+    for world in (2, 3, 4, 8):
+        for rings in (1, 2):
+            for n in (4 * world, 4 * 12345, ll_max // 4):
+                used = lib.ldnn_ring_ll_slots(n, world, rings)
+                assert 0 < used <= phase4, (n, world, rings, used)
