@@ -112,7 +112,7 @@ struct Launch {
 struct Plan {
   int mode, block_n, cluster = 1, lite = 0;
   int tf32 = 0;                             // fp32 storage + kind::tf32 (desc.dtype == 1)
-  int pair = 0;                             // cluster == 2 run as a cta_group::2 pair (desc.cluster == -2; staged)
+  int pair = 0;                             // cluster == 2 run as a cta_group::2 pair (desc.cluster == -2)
   std::vector<Launch> launches;
   void* out;
   const void* addend;
@@ -410,7 +410,7 @@ template <typename ET, int MODE>
 static int launch_bn(const Launch& L, const Plan& pl, cudaStream_t st) {
   if (pl.cluster == 2 && MODE != MODE_WGRAD) {      // cluster path: 128/256-wide tiles, full pipeline
     constexpr int M2 = MODE == MODE_WGRAD ? MODE_FPROP : MODE;
-    if (pl.pair) {                                   // cta_group::2 pair (UMMA_M = 256), staged
+    if (pl.pair) {                                   // cta_group::2 pair (UMMA_M = 256)
       if (pl.block_n == 128) return launch_one<ET, M2, 128, -2, false>(L, pl, st);
       return launch_one<ET, M2, 256, -2, false>(L, pl, st);
     }

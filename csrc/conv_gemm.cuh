@@ -119,7 +119,7 @@ struct ConvCfg {
 // multicasts it into both CTAs' shared memory, halving the L2 reads of the operand both need; a smem
 // stage is recycled only when both CTAs' MMAs have drained it (multicast tcgen05.commit).
 // LITE = short pipeline + 4 epilogue warps, two CTAs per SM (large grids of short-K tiles).
-// CL = -2 ("pair", staged — see NEXT.md 1a): the two CTAs of a TPC run ONE tcgen05.mma.cta_group::2 of UMMA_M = 256:
+// CL = -2 ("pair"; run on hardware in round 2, both precisions): the two CTAs of a TPC run ONE tcgen05.mma.cta_group::2 of UMMA_M = 256:
 // each CTA loads its own A box and only ITS HALF of the B tile (no multicast: half the B bytes enter each SM), the
 // leader CTA issues the MMAs for both, each CTA's TMEM receives its own 128 rows and its epilogue is unchanged.
 template <typename ET, int MODE, int BLOCK_N, int CL, bool LITE>

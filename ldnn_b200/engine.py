@@ -203,7 +203,7 @@ class TorchEngine(Engine):
         def alloc(n):
             name = ["params", "grads", "m", "v"][len(self._symm)]
             if name in ("params", "grads") and K.nvls_requested():
-                t, handle, ptr = K.symm_alloc_multicast(n * 4, self.device)      # LDNN_NVLS=1 (staged)
+                t, handle, ptr = K.symm_alloc_multicast(n * 4, self.device)      # multicast-capable slab (NVLS all-reduce); IPC slab if unavailable
             else:
                 t, handle, ptr = K.symm_alloc(n * 4, self.device)
             self._symm[name] = (t, handle, ptr)

@@ -2,7 +2,8 @@
 
 Every function launches on the *current* torch CUDA stream, so the calls compose with
 ``torch.cuda.graph`` capture and with side streams.  Layout conventions:
-activations NHWC bf16, conv weights KRSC bf16 (``[Cout][R*S*Cin]``), statistics fp32.
+activations NHWC, conv weights KRSC (``[Cout][R*S*Cin]``), statistics fp32; the element type of the activation
+tensors selects the kernel family — bfloat16 (``kind::f16`` MMA) or float32 (``kind::tf32`` MMA, ``_f32`` entry points).
 """
 from __future__ import annotations
 
