@@ -239,6 +239,13 @@ class CompatExchanger(DistExchanger):
         return super().exchange_(t)
 
 
+def shutdown():
+    """Release what the exchange functions of this module allocated on the GPU (symmetric staging slab, signal pads).
+    Collective; optional — for long-lived hosts that keep the process after training."""
+    from .parallel.fused import StagedFusedExchange
+    StagedFusedExchange.close_all()
+
+
 def _ex(topology, kind, world_size, local_weight=0.5, rank=None):
     r = rank if rank is not None else (dist.get_rank() if dist.is_initialized() else 0)
     sem = "allreduce" if topology == "allreduce" else "gossip"

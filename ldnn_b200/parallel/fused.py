@@ -528,6 +528,16 @@ class StagedFusedExchange:
         return t
 
     @classmethod
+    def close_all(cls) -> None:
+        """Collective: unmap and free every staging slab / signal pad the reference-signature entry points created
+        (call on every rank before the process group is destroyed; a later exchange builds them again)."""
+        for inst in list(cls._instances.values()):
+            for ex in inst.ex.values():
+                ex.close()
+            inst.ex, inst.eng, inst.cap = {}, None, 0
+        cls._instances.clear()
+
+    @classmethod
     def usable(cls, rt, t: torch.Tensor) -> bool:
         """Single-node NCCL job, fp32 CUDA tensor, at most LDNN_MAX_RANKS ranks, library present."""
         if not (t.is_cuda and t.dtype == torch.float32 and dist.is_available() and dist.is_initialized()):

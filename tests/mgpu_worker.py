@@ -124,6 +124,10 @@ def main():
             want = (M @ X)[r].view(shape).to(dev)
             assert float((t.double() - want).abs().max()) < 1e-5, (topo, kind, shape)
     assert L.launch_count() > launched0, "compat exchange did not launch our kernels"
+    compat.shutdown()                                   # frees the staging slab and pads (collective)
+    t = torch.ones(8, device=dev)
+    compat.ring_all_reduce_equal(t, r, ws)              # ... and the next call simply builds them again
+    assert float((t - 1).abs().max()) < 1e-6
 
     # broadcast
     sp = ExchangeSpec("allreduce", "allreduce", "equal", 0.5, None, ws)
