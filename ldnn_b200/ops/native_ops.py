@@ -415,7 +415,10 @@ def symm_rendezvous(t: torch.Tensor):
     import torch.distributed._symmetric_memory as symm_mem
     group = dist.group.WORLD
     try:
-        symm_mem.enable_symm_mem_for_group(group.group_name)        # needed by older torch, harmless otherwise
+        import warnings
+        with warnings.catch_warnings():                              # deprecated (a no-op) in current torch
+            warnings.simplefilter("ignore")
+            symm_mem.enable_symm_mem_for_group(group.group_name)    # needed by older torch, harmless otherwise
     except Exception:
         pass
     hdl = symm_mem.rendezvous(t, group)

@@ -231,3 +231,22 @@ def test_checkpoint_keeps_every_ranks_own_replica(tmp_path):
     k0 = fresh.flat.slots[0].key
     assert torch.equal(fresh.flat.view(fresh.flat.params, k0), engs[0].flat.view(engs[0].flat.params, k0))
     assert any("replica" in str(x.message) for x in w)
+
+
+def test_bench_arms_emit_the_same_config_keys():
+    """The driver compares the two arms' `config` objects: both come from one function, arm-specific facts go to `extra`."""
+    import importlib.util
+    import os
+    import types
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_main", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    a = types.SimpleNamespace(model="enhanced_cnn", batch=64, aggregation_type="equal", shard_ratios=None)
+    ours = bench.config_block(a, 8, 512, "allreduce", "global_epoch")
+    ref = bench.config_block(a, 8, 512, "allreduce", "global_epoch")
+    assert ours == ref and {"model", "global_batch", "parallelism", "topology", "sync", "l2"} <= set(ours)
+    assert ours["parallelism"] == "dp8" and ours["global_batch"] == 512
+    assert bench.DTYPE_HEADLINE == "tf32"
+    assert bench.ratios_for(types.SimpleNamespace(shard_ratios=None), 4) == [1.0] * 4
+    assert bench.ratios_for(types.SimpleNamespace(shard_ratios=[4, 2, 1, 1]), 4) == [4.0, 2.0, 1.0, 1.0]
