@@ -42,10 +42,11 @@ def test_state_dict_roundtrip_reference_layout(dt):
 # batch through the randomly initialised 21-layer net, and for the loss.  tf32 keeps fp32 storage and only rounds
 # the MMA operands to 11 significand bits; bf16 also rounds every stored activation to 8 bits, and the rounding
 # noise is amplified layer by layer on the way down (deepest = first layers): measured worst tensor 0.912-0.923 for the
-# native bf16 engine, 0.924 for torch's own bf16 autocast of the same model (printed by the test) — hence 0.90.
+# native bf16 engine over a dozen runs (0.905 once: the fp32 atomics make runs differ), 0.924 for torch's own bf16
+# autocast of the same model (printed by the test) — hence 0.88.
 # tf32: measured worst tensor 0.990-0.993 (layer1 BN biases, the far end of backward) — the same place and size as
 # torch's own TF32 run of the model (cuDNN TF32 convolutions, what the reference executes), printed as `yard`.
-FLOORS = {"tf32": dict(cos=0.985, ratio=0.03, loss=2e-3), "bf16": dict(cos=0.90, ratio=0.15, loss=3e-2)}
+FLOORS = {"tf32": dict(cos=0.985, ratio=0.03, loss=2e-3), "bf16": dict(cos=0.88, ratio=0.15, loss=3e-2)}
 
 
 @pytest.mark.parametrize("dt", DT)
