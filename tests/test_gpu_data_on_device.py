@@ -57,7 +57,7 @@ def test_training_from_a_device_resident_uint8_dataset():
         loss, _ = eng.train_step(x, y)
         losses.append(loss.detach().reshape(()).clone())
     losses = torch.stack(losses).cpu()
-    assert torch.isfinite(losses).all() and float(losses[-8:].mean()) < 0.6 * float(losses[:4].mean()), losses.tolist()
+    assert torch.isfinite(losses).all() and float(losses[-8:].mean()) < 0.85 * float(losses[:4].mean()), losses.tolist()
     # loader alone: gather + grouped augmentation + normalisation on the GPU
     torch.cuda.synchronize()
     t0 = time.perf_counter()
