@@ -58,3 +58,52 @@ def test_b1_b6_what_the_exchange_reaches(dist_runner, tmp_path, mode):
         assert torch.allclose(a["params"], b["params"], atol=1e-6)
     # B6: running statistics are per rank in every mode (different shards, never exchanged after the broadcast)
     assert not torch.allclose(a["bn_mean"], b["bn_mean"], atol=1e-7)
+
+
+def _shard_weight_worker(rank, world, out_dir):
+    os.environ["LDNN_TINY_WIDTHS"] = "1"
+    import json
+    from ldnn_b200 import data as D
+    from ldnn_b200.config import Config, resolve
+    from ldnn_b200.engine import make_engine
+    from ldnn_b200.launch import init_runtime, shutdown
+    from ldnn_b200.parallel import make_exchanger
+    from ldnn_b200.trainer import refresh_shard_weights, train_global
+    # no explicit --shard_ratios: shard sizes follow the timing-derived ratios and move at every re-shard
+    cfg = resolve(Config(backend="gloo", synthetic=True, synthetic_train=160, synthetic_val=32, synthetic_test=32,
+                         epochs_global=3, epochs_local=1, batch_size=16, probe_batches=1, seed=5, quiet=True,
+                         topology="allreduce", engine="torch", exchange_impl="dist", aggregation_type="shard",
+                         aggregation_by="weights", output_folder=out_dir))
+    rt = init_runtime("gloo", seed=cfg.seed)
+    engine = make_engine(cfg, rt)
+    bundle = D.get_data(cfg, rt.rank)
+    ex = make_exchanger(cfg, rt, engine)
+    ex.broadcast_state(engine, src=0)
+    shards = D.initial_shards(bundle, cfg, rt, engine)
+    refresh_shard_weights(cfg, rt, shards, ex)
+    seen = []
+
+    def on_epoch_end(ge, h, sh):
+        sizes = D.all_gather_floats(float(len(sh.train_indices)), rt)
+        seen.append({"sizes": sizes, "weights": list(ex.spec.shard_weights)})
+
+    train_global(engine, bundle, shards, cfg, rt, ex, on_epoch_end=on_epoch_end)
+    if rank == 0:
+        with open(os.path.join(out_dir, "shard_weights.json"), "w") as f:
+            json.dump(seen, f)
+    ex.close()
+    shutdown(rt)
+
+
+def test_shard_weights_follow_the_shards_across_reshards(dist_runner, tmp_path):
+    """--aggregation_type shard: w_r = n_r / sum(n) of the shards the ranks hold NOW — re-computed after every re-shard
+    (the sizes follow ratio x total and move with the measured epoch durations), not frozen at start-up."""
+    import json
+    dist_runner(_shard_weight_worker, 2, str(tmp_path))
+    seen = json.load(open(tmp_path / "shard_weights.json"))
+    assert len(seen) == 3
+    for e in seen:
+        tot = sum(e["sizes"])
+        assert tot > 0 and abs(sum(e["weights"]) - 1.0) < 1e-9
+        for w, n in zip(e["weights"], e["sizes"]):
+            assert abs(w - n / tot) < 1e-9, e
