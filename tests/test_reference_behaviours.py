@@ -107,3 +107,40 @@ def test_shard_weights_follow_the_shards_across_reshards(dist_runner, tmp_path):
         assert tot > 0 and abs(sum(e["weights"]) - 1.0) < 1e-9
         for w, n in zip(e["weights"], e["sizes"]):
             assert abs(w - n / tot) < 1e-9, e
+
+
+def _empty_shard_worker(rank, world, out_dir):
+    os.environ["LDNN_TINY_WIDTHS"] = "1"
+    from ldnn_b200 import data as D
+    from ldnn_b200.config import Config, resolve
+    from ldnn_b200.engine import make_engine
+    from ldnn_b200.launch import init_runtime, shutdown
+    from ldnn_b200.parallel import make_exchanger
+    from ldnn_b200.trainer import train_global
+    cfg = resolve(Config(backend="gloo", synthetic=True, synthetic_train=64, synthetic_val=32, synthetic_test=32,
+                         epochs_global=1, epochs_local=1, batch_size=16, probe_batches=1, seed=5, quiet=True, sync="step",
+                         topology="allreduce", engine="torch", exchange_impl="dist", shard_ratios=[1000.0, 1.0],
+                         output_folder=out_dir))
+    rt = init_runtime("gloo", seed=cfg.seed)
+    engine = make_engine(cfg, rt)
+    bundle = D.get_data(cfg, rt.rank)
+    ex = make_exchanger(cfg, rt, engine)
+    shards = D.initial_shards(bundle, cfg, rt, engine)
+    msg = "no error"
+    try:
+        train_global(engine, bundle, shards, cfg, rt, ex)
+    except RuntimeError as e:
+        msg = str(e)
+    with open(os.path.join(out_dir, f"empty_{rank}.txt"), "w") as f:
+        f.write(f"{len(shards.train_indices)}|{msg}")
+    shutdown(rt)
+
+
+def test_per_step_schedule_reports_an_empty_shard_instead_of_hanging(dist_runner, tmp_path):
+    """--sync step: every step is a collective, so a rank with nothing to feed it would leave its peers waiting.  All
+    ranks see the same minimum shard length and stop together with a clear error."""
+    dist_runner(_empty_shard_worker, 2, str(tmp_path))
+    out = [open(tmp_path / f"empty_{r}.txt").read().split("|", 1) for r in range(2)]
+    assert int(out[1][0]) == 0 and int(out[0][0]) > 0            # ratios 1000:1 of 64 samples: rank 1 holds nothing
+    for n, msg in out:
+        assert "empty training shard" in msg, msg
